@@ -1,0 +1,623 @@
+// Implicit-GEMM convolution on the 5th-generation tensor cores (sm_100a): tcgen05.mma with the
+// accumulator in TMEM, operands staged in shared memory by TMA, fused epilogue
+// (bias, ReLU, residual add, optional second "BN+ReLU'd" output) written back with TMA stores.
+//
+//   D[M = pixels][N = Cout] = A[M][K] * W[N][K]^T,   K ordered (ky, kx, cin)
+//
+// * No im2col buffer exists anywhere.  The activation tensor is NHWC; one K-block of A for tap
+//   (ky,kx) and channel block cb is a 4-D TMA box {64 ch, bw, bh, bn} of the input at the shifted
+//   (and, for stride 2, element-strided) position.  Out-of-bounds coordinates are zero-filled by
+//   the TMA unit, which *is* the conv's zero padding.  The M tile is therefore a spatial patch
+//   bw x bh of bn images (bw*bh*bn <= 128), chosen per layer and batch to fill the 128-row MMA.
+// * The 7x7/2 stem (3 input channels) uses a 5-D overlapping-stride view of a zero-framed
+//   [B,230,232,4] input: one K-block per filter row = 8 consecutive pixels x 4 channels = 64 bytes
+//   (SWIZZLE_64B), so K = 7 x 32 with the 8th pixel / 4th channel multiplied by zero weights.
+// * Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread
+//   tcgen05.mma issuer, warps 2-5 = epilogue (TMEM -> registers -> swizzled smem -> TMA store).
+//   One output tile per CTA; shared memory is sized so two CTAs share an SM and one CTA's
+//   epilogue overlaps the other's main loop.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+
+namespace rn {
+namespace {
+
+constexpr int kThreads = 192;
+constexpr int kTileM = 128;
+constexpr int kChunkBytes = kTileM * 128;  // one 64-channel output chunk of a tile (16 KB)
+
+struct UmmaParams {
+  int num_k_iters, cblks, kw, stride, pad, stem;
+  int bw, bh, bn, tiles_w, tiles_h;
+  int n_tiles, num_stages;
+  int has_res, has_out, has_act, relu, act_relu;
+  uint32_t a_bytes, b_bytes, rows;
+  const float* bias;
+  const float* act_scale;
+  const float* act_shift;
+};
+
+// ---- PTX wrappers -----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// Set when a barrier wait gives up (a mis-sized TMA transaction would otherwise hang the GPU);
+// the host checks it after the stream is synchronised and reports an error instead of results.
+__device__ unsigned int g_umma_timeout = 0;
+
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, P1;\n\t"
+      "}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 1000000000LL) {  // ~0.5 s at 2 GHz: never reached by a healthy launch
+      atomicExch(&g_umma_timeout, 1u);
+      return;
+    }
+  }
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+               ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2, int c3, int c4) {
+  asm volatile("cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+               ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4) : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t slot_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot_smem), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t"
+      ".reg .b32 rx;\n\t"
+      ".reg .pred px;\n\t"
+      "elect.sync rx|px, %1;\n\t"
+      "@px mov.s32 %0, 1;\n\t"
+      "}" : "+r"(pred) : "r"(0xffffffffu));
+  return pred != 0;
+}
+
+// K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+//  [0,14) start>>4 | [16,30) LBO>>4 (unused for swizzled K-major) | [32,46) SBO>>4 = 8 rows of the
+//  swizzle atom | [46,48) version = 1 | [61,64) layout: 2 = SWIZZLE_128B, 4 = SWIZZLE_64B
+template <int KB>
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  constexpr uint64_t layout = (KB == 128) ? 2 : 4;
+  constexpr uint64_t sbo = (8 * KB) >> 4;
+  return uint64_t((smem_addr & 0x3FFFF) >> 4) | (uint64_t(1) << 16) | (sbo << 32) | (uint64_t(1) << 46) | (layout << 61);
+}
+
+template <typename T> struct Fmt;
+template <> struct Fmt<__nv_bfloat16> { static constexpr uint32_t id = 1; };
+template <> struct Fmt<__half> { static constexpr uint32_t id = 0; };
+
+// cute::UMMA::InstrDescriptor: c_format F32 (bit 4) | a_format [7,10) | b_format [10,13) |
+// a/b K-major (bits 15,16 = 0) | N>>3 at [17,23) | M>>4 at [24,29)
+template <typename T, int N>
+__device__ __forceinline__ constexpr uint32_t make_idesc() {
+  return (1u << 4) | (Fmt<T>::id << 7) | (Fmt<T>::id << 10) | (uint32_t(N >> 3) << 17) | (uint32_t(kTileM >> 4) << 24);
+}
+
+template <typename T> __device__ __forceinline__ uint32_t pack2(float a, float b);
+template <> __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+template <> __device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+template <typename T> __device__ __forceinline__ float2 unpack2(uint32_t u);
+template <> __device__ __forceinline__ float2 unpack2<__nv_bfloat16>(uint32_t u) {
+  return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u));
+}
+template <> __device__ __forceinline__ float2 unpack2<__half>(uint32_t u) {
+  return __half22float2(*reinterpret_cast<__half2*>(&u));
+}
+
+// ---- the kernel -------------------------------------------------------------------------------
+// Dynamic shared memory (1024-byte aligned):
+//   [pipeline: num_stages x (A tile | B tile)]   reused as output staging once the MMAs are done
+//   [residual: BLOCK_N/64 x 16 KB]               only when has_res; raw output is staged in place
+//   [params:   3 x BLOCK_N floats][barriers][tmem slot]
+template <typename T, int BLOCK_N, int KB>
+__global__ void __launch_bounds__(kThreads)
+conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                 const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
+                 const __grid_constant__ CUtensorMap tmAct, const UmmaParams p, const uint32_t pipe_bytes) {
+  constexpr int kChunks = BLOCK_N / 64;
+  constexpr int kMmaPerBlock = KB / 32;        // UMMA_K = 16 elements = 32 bytes
+  constexpr uint32_t A_BYTES = kTileM * KB;
+  constexpr uint32_t B_BYTES = BLOCK_N * KB;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* pipe = smem;
+  uint8_t* resbuf = smem + pipe_bytes;
+  uint8_t* tail = resbuf + (p.has_res ? kChunks * kChunkBytes : 0);
+  float* s_bias = reinterpret_cast<float*>(tail);
+  float* s_scale = s_bias + BLOCK_N;
+  float* s_shift = s_scale + BLOCK_N;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_shift + BLOCK_N);
+  // bars[0..S) full, bars[S..2S) empty, bars[2S] tmem_full, bars[2S+1] res_full
+  const int S = p.num_stages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile = blockIdx.x;
+  const int n_tile = tile % p.n_tiles;
+  int mt = tile / p.n_tiles;
+  const int tw = mt % p.tiles_w; mt /= p.tiles_w;
+  const int th = mt % p.tiles_h;
+  const int tn = mt / p.tiles_h;
+  const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
+  const int col0 = n_tile * BLOCK_N;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmW);
+    if (p.has_res) prefetch_tmap(&tmRes);
+    if (p.has_out) prefetch_tmap(&tmOut);
+    if (p.has_act) prefetch_tmap(&tmAct);
+    for (int i = 0; i < S; ++i) {
+      mbar_init(smem_u32(&bars[i]), 1);
+      mbar_init(smem_u32(&bars[S + i]), 1);
+    }
+    mbar_init(smem_u32(&bars[2 * S]), 1);
+    mbar_init(smem_u32(&bars[2 * S + 1]), 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), BLOCK_N);
+  if (warp >= 2) {
+    for (int i = threadIdx.x - 64; i < BLOCK_N; i += 128) {
+      s_bias[i] = __ldg(p.bias + col0 + i);
+      s_scale[i] = p.has_act ? __ldg(p.act_scale + col0 + i) : 1.f;
+      s_shift[i] = p.has_act ? __ldg(p.act_shift + col0 + i) : 0.f;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (elect_one()) {
+      if (p.has_res) {
+        const uint32_t rb = smem_u32(&bars[2 * S + 1]);
+        mbar_expect_tx(rb, p.rows * 128u * kChunks);
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c)
+          tma_load_4d(smem_u32(resbuf + c * kChunkBytes), &tmRes, rb, col0 + c * 64, w0, h0, n0);
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int it = 0; it < p.num_k_iters; ++it) {
+        mbar_wait(smem_u32(&bars[S + stage]), phase ^ 1);
+        const uint32_t fb = smem_u32(&bars[stage]);
+        const uint32_t a_dst = smem_u32(pipe + stage * STAGE_BYTES);
+        mbar_expect_tx(fb, p.a_bytes + p.b_bytes);
+        if (p.stem) {
+          tma_load_5d(a_dst, &tmA, fb, 0, w0, it & 1, h0 + (it >> 1), n0);
+        } else {
+          const int tap = it / p.cblks, cb = it - tap * p.cblks;
+          const int ky = tap / p.kw, kx = tap - ky * p.kw;
+          tma_load_4d(a_dst, &tmA, fb, cb * 64, w0 * p.stride - p.pad + kx, h0 * p.stride - p.pad + ky, n0);
+        }
+        tma_load_2d(a_dst + A_BYTES, &tmW, fb, it * (KB / 2), col0);
+        if (++stage == S) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one elected thread) =====
+    constexpr uint32_t idesc = make_idesc<T, BLOCK_N>();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int it = 0; it < p.num_k_iters; ++it) {
+      mbar_wait(smem_u32(&bars[stage]), phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t a_addr = smem_u32(pipe + stage * STAGE_BYTES);
+        const uint32_t b_addr = a_addr + A_BYTES;
+#pragma unroll
+        for (int k = 0; k < kMmaPerBlock; ++k) {
+          const uint64_t da = make_smem_desc<KB>(a_addr + k * 32);
+          const uint64_t db = make_smem_desc<KB>(b_addr + k * 32);
+          umma_f16(tmem_base, da, db, idesc, (it | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(smem_u32(&bars[S + stage]));                              // frees the smem slot
+        if (it == p.num_k_iters - 1) umma_commit(smem_u32(&bars[2 * S]));      // accumulator complete
+      }
+      __syncwarp();
+      if (++stage == S) { stage = 0; phase ^= 1; }
+    }
+  } else {
+    // ===== epilogue: 4 warps, thread = one output pixel (TMEM lane) =====
+    const int q = warp & 3;                 // TMEM lane quarter this warp may access
+    const int row = q * 32 + lane;
+    mbar_wait(smem_u32(&bars[2 * S]), 0);
+    tc_fence_after();
+    if (p.has_res) mbar_wait(smem_u32(&bars[2 * S + 1]), 0);
+    const int sw = row & 7;
+#pragma unroll 1
+    for (int c = 0; c < kChunks; ++c) {
+      uint32_t acc[64];
+      {
+        uint32_t (&lo)[32] = *reinterpret_cast<uint32_t (*)[32]>(&acc[0]);
+        uint32_t (&hi)[32] = *reinterpret_cast<uint32_t (*)[32]>(&acc[32]);
+        const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(c * 64);
+        tmem_ld_32x32b_x32(taddr, lo);
+        tmem_ld_32x32b_x32(taddr + 32, hi);
+        tmem_ld_wait();
+      }
+      uint8_t* raw_stage = p.has_res ? (resbuf + c * kChunkBytes) : (pipe + (2 * c) * kChunkBytes);
+      uint8_t* act_stage = pipe + (2 * c + 1) * kChunkBytes;
+      uint4* raw_row = reinterpret_cast<uint4*>(raw_stage + row * 128);
+      uint4* act_row = reinterpret_cast<uint4*>(act_stage + row * 128);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {           // 8 channels (16 bytes) at a time
+        float v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          v[i] = __uint_as_float(acc[j * 8 + i]) + s_bias[c * 64 + j * 8 + i];
+          if (p.relu) v[i] = fmaxf(v[i], 0.f);
+        }
+        const int slot = j ^ sw;              // SWIZZLE_128B: 16-byte chunk index XOR (row mod 8)
+        if (p.has_res) {
+          const uint4 r = raw_row[slot];
+          const float2 r0 = unpack2<T>(r.x), r1 = unpack2<T>(r.y), r2 = unpack2<T>(r.z), r3 = unpack2<T>(r.w);
+          v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
+          v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
+        }
+        if (p.has_out)
+          raw_row[slot] = make_uint4(pack2<T>(v[0], v[1]), pack2<T>(v[2], v[3]), pack2<T>(v[4], v[5]), pack2<T>(v[6], v[7]));
+        if (p.has_act) {
+          float a[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            a[i] = fmaf(s_scale[c * 64 + j * 8 + i], v[i], s_shift[c * 64 + j * 8 + i]);
+            if (p.act_relu) a[i] = fmaxf(a[i], 0.f);
+          }
+          act_row[slot] = make_uint4(pack2<T>(a[0], a[1]), pack2<T>(a[2], a[3]), pack2<T>(a[4], a[5]), pack2<T>(a[6], a[7]));
+        }
+      }
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) {
+        if (p.has_out) tma_store_4d(&tmOut, smem_u32(raw_stage), col0 + c * 64, w0, h0, n0);
+        if (p.has_act) tma_store_4d(&tmAct, smem_u32(act_stage), col0 + c * 64, w0, h0, n0);
+        tma_store_commit();
+      }
+    }
+    if (warp == 2 && lane == 0) tma_store_wait_read();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, BLOCK_N);
+}
+
+// ---- host side --------------------------------------------------------------------------------
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+bool encode(CUtensorMap* m, DType dt, int rank, const void* base, const uint64_t* dims, const uint64_t* strides_bytes,
+            const uint32_t* box, const uint32_t* estr, bool sw64, std::string& err) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) { err = "cuTensorMapEncodeTiled is not available from the driver"; return false; }
+  cuuint64_t d[5]; cuuint64_t s[4]; cuuint32_t b[5], e[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = estr[i]; }
+  for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
+  CUresult r = fn(m, dt == DType::BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                  cuuint32_t(rank), const_cast<void*>(base), d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  sw64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[256];
+    std::snprintf(buf, sizeof buf, "cuTensorMapEncodeTiled failed (CUresult %d) rank=%d dims=[%llu,%llu,%llu,%llu] box=[%u,%u,%u,%u]",
+                  int(r), rank, (unsigned long long)dims[0], (unsigned long long)dims[1],
+                  (unsigned long long)(rank > 2 ? dims[2] : 0), (unsigned long long)(rank > 3 ? dims[3] : 0), box[0], box[1],
+                  rank > 2 ? box[2] : 0, rank > 3 ? box[3] : 0);
+    err = buf;
+    return false;
+  }
+  return true;
+}
+
+// NHWC activation [B,H,W,C] as a 4-D map (C, W, H, N) with a {64, bw*es, bh*es, bn} box
+bool encode_act(CUtensorMap* m, DType dt, const void* base, int B, int H, int W, int C, int bw, int bh, int bn, int es,
+                std::string& err) {
+  uint64_t dims[4] = {uint64_t(C), uint64_t(W), uint64_t(H), uint64_t(B)};
+  uint64_t str[3] = {uint64_t(C) * 2, uint64_t(W) * C * 2, uint64_t(H) * W * C * 2};
+  uint32_t box[4] = {64, uint32_t(bw * es), uint32_t(bh * es), uint32_t(bn)};
+  uint32_t estr[4] = {1, uint32_t(es), uint32_t(es), 1};
+  return encode(m, dt, 4, base, dims, str, box, estr, false, err);
+}
+
+}  // namespace
+
+// Stem frame geometry (fast path): image at (3,3) inside [Hp, Wp] with zero borders.
+static inline int stem_Hp(int H) { return H + 6; }
+static inline int stem_Wp(int W) { return ((W + 3 + 5) + 7) / 8 * 8; }
+
+struct UmmaConvPlan {
+  DType dt;
+  ConvGeom g;
+  int stem;
+  int block_n, kb;
+  UmmaParams p;
+  CUtensorMap tmA, tmW, tmRes, tmOut, tmAct;
+  uint32_t pipe_bytes, smem_bytes;
+  int grid;
+};
+
+bool umma_conv_supported(const ConvGeom& g, int stem_mode, char* why, size_t cap) {
+  auto no = [&](const char* m) { if (why && cap) std::snprintf(why, cap, "%s", m); return false; };
+  if (stem_mode) {
+    if (!(g.kh == 7 && g.kw == 7 && g.stride == 2 && g.pad == 3 && g.Cin == 4 && g.Cout % 64 == 0))
+      return no("stem path needs a 7x7/2 pad-3 conv on a 4-channel (3 padded) input with Cout % 64 == 0");
+    return true;
+  }
+  if (g.Cin % 64 || g.Cout % 64) return no("tensor-core conv needs Cin % 64 == 0 and Cout % 64 == 0");
+  if (g.stride != 1 && g.stride != 2) return no("tensor-core conv supports stride 1 or 2");
+  if (g.kh != g.kw) return no("tensor-core conv needs a square filter");
+  return true;
+}
+
+size_t umma_weight_bytes(const ConvGeom& g, int stem_mode) {
+  if (stem_mode) return size_t(g.Cout) * 7 * 32 * 2;
+  return size_t(g.Cout) * g.kh * g.kw * g.Cin * 2;
+}
+
+template <typename T> static T host_cvt(float f);
+template <> __nv_bfloat16 host_cvt<__nv_bfloat16>(float f) { return __float2bfloat16_rn(f); }
+template <> __half host_cvt<__half>(float f) { return __float2half_rn(f); }
+
+template <typename T>
+static void pack_weights_t(const float* w, const ConvGeom& g, int stem_mode, T* dst) {
+  if (!stem_mode) {
+    size_t n = size_t(g.Cout) * g.kh * g.kw * g.Cin;   // already [Cout][ky][kx][Cin] = K-major
+    for (size_t i = 0; i < n; ++i) dst[i] = host_cvt<T>(w[i]);
+    return;
+  }
+  // stem: [Cout][ky 0..6][kx 0..7][c 0..3]; kx = 7 is zero (8-pixel granule), c = 3 is the pad channel
+  for (int o = 0; o < g.Cout; ++o)
+    for (int ky = 0; ky < 7; ++ky)
+      for (int kx = 0; kx < 8; ++kx)
+        for (int c = 0; c < 4; ++c) {
+          float v = (kx < 7) ? w[((size_t(o) * 7 + ky) * 7 + kx) * g.Cin + c] : 0.f;
+          dst[((size_t(o) * 7 + ky) * 8 + kx) * 4 + c] = host_cvt<T>(v);
+        }
+}
+
+void umma_pack_weights(const float* w, const ConvGeom& g, DType dt, int stem_mode, void* dst) {
+  if (dt == DType::BF16) pack_weights_t<__nv_bfloat16>(w, g, stem_mode, static_cast<__nv_bfloat16*>(dst));
+  else pack_weights_t<__half>(w, g, stem_mode, static_cast<__half*>(dst));
+}
+
+// pick the spatial patch (bw x bh of bn images) that wastes the fewest MMA rows
+static void choose_patch(int B, int Ho, int Wo, int& bw, int& bh, int& bn) {
+  double best = -1;
+  for (int w = 1; w <= Wo && w <= kTileM; ++w)
+    for (int h = 1; h <= Ho && w * h <= kTileM; ++h) {
+      int n = kTileM / (w * h);
+      if (n > B) n = B;
+      if (n > 256) n = 256;
+      long tiles = long((Wo + w - 1) / w) * ((Ho + h - 1) / h) * ((B + n - 1) / n);
+      double eff = double(B) * Ho * Wo / (double(tiles) * kTileM);
+      // prefer wider patches on ties (longer contiguous runs per TMA box)
+      if (eff > best + 1e-9 || (eff > best - 1e-9 && w > bw)) { best = eff; bw = w; bh = h; bn = n; }
+    }
+}
+
+template <typename T, int BLOCK_N, int KB>
+static cudaError_t launch_inst(const UmmaConvPlan* pl, cudaStream_t s) {
+  auto kern = conv_umma_kernel<T, BLOCK_N, KB>;
+  static thread_local int configured_device = -1;  // per (instantiation, thread)
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    configured_device = dev;
+  }
+  kern<<<pl->grid, kThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->p, pl->pipe_bytes);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
+  const bool bf = pl->dt == DType::BF16;
+  if (pl->kb == 64) return bf ? launch_inst<__nv_bfloat16, 64, 64>(pl, s) : launch_inst<__half, 64, 64>(pl, s);
+  if (pl->block_n == 64) return bf ? launch_inst<__nv_bfloat16, 64, 128>(pl, s) : launch_inst<__half, 64, 128>(pl, s);
+  return bf ? launch_inst<__nv_bfloat16, 128, 128>(pl, s) : launch_inst<__half, 128, 128>(pl, s);
+}
+
+UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in, const void* w_packed,
+                                    const Epilogue& e, int stem_mode, char* err, size_t errcap) {
+  auto failmsg = [&](const std::string& m) -> UmmaConvPlan* {
+    if (err && errcap) std::snprintf(err, errcap, "%s", m.c_str());
+    return nullptr;
+  };
+  char why[200];
+  if (dt == DType::F32) return failmsg("tensor-core conv needs a 16-bit activation type");
+  if (!umma_conv_supported(g, stem_mode, why, sizeof why)) return failmsg(why);
+  auto pl = new UmmaConvPlan();
+  pl->dt = dt; pl->g = g; pl->stem = stem_mode;
+  pl->kb = stem_mode ? 64 : 128;
+  pl->block_n = (stem_mode || g.Cout % 128) ? 64 : 128;
+  UmmaParams& p = pl->p;
+  std::memset(&p, 0, sizeof p);
+  int bw = 0, bh = 0, bn = 0;
+  choose_patch(g.B, g.Ho, g.Wo, bw, bh, bn);
+  p.bw = bw; p.bh = bh; p.bn = bn;
+  p.tiles_w = (g.Wo + bw - 1) / bw;
+  p.tiles_h = (g.Ho + bh - 1) / bh;
+  int tiles_n = (g.B + bn - 1) / bn;
+  p.n_tiles = g.Cout / pl->block_n;
+  p.rows = uint32_t(bw * bh * bn);
+  p.stem = stem_mode; p.kw = g.kw; p.stride = g.stride; p.pad = g.pad;
+  p.cblks = stem_mode ? 1 : g.Cin / 64;
+  p.num_k_iters = stem_mode ? 7 : g.kh * g.kw * p.cblks;
+  p.a_bytes = p.rows * uint32_t(pl->kb);
+  p.b_bytes = uint32_t(pl->block_n * pl->kb);
+  p.has_res = e.residual != nullptr; p.has_out = e.out != nullptr; p.has_act = e.out_act != nullptr;
+  p.relu = e.relu; p.act_relu = e.act_relu;
+  p.bias = e.bias; p.act_scale = e.act_scale; p.act_shift = e.act_shift;
+  if (!p.has_out && !p.has_act) { delete pl; return failmsg("conv with no output"); }
+
+  const uint32_t stage_bytes = uint32_t(kTileM * pl->kb + pl->block_n * pl->kb);
+  const int chunks = pl->block_n / 64;
+  const uint32_t staging = uint32_t(2 * chunks) * kChunkBytes;
+  const uint32_t res_bytes = p.has_res ? uint32_t(chunks) * kChunkBytes : 0;
+  const uint32_t tail_bytes = 3u * uint32_t(pl->block_n) * 4 + 8u * (2 * 8 + 2) + 16;
+  // deepest pipeline that still lets two CTAs share an SM (2 x ~113 KB), at least 2, at most 6
+  int stages = 6;
+  auto total = [&](int s) { return 1024u + std::max(uint32_t(s) * stage_bytes, staging) + res_bytes + tail_bytes; };
+  while (stages > 2 && total(stages) > 113u * 1024) --stages;
+  if (stages > p.num_k_iters) stages = std::max(1, p.num_k_iters);
+  p.num_stages = stages;
+  pl->pipe_bytes = std::max(uint32_t(stages) * stage_bytes, staging);
+  pl->smem_bytes = 1024u + pl->pipe_bytes + res_bytes + tail_bytes;
+  pl->grid = p.tiles_w * p.tiles_h * tiles_n * p.n_tiles;
+
+  std::string msg;
+  bool ok = true;
+  if (stem_mode) {
+    // 5-D overlapping view of the zero-framed input [B, Hp, Wp, 4]:
+    //   d0 = 32 elements (8 px x 4 ch), d1 = output column (stride 2 px = 16 B), d2 = row parity,
+    //   d3 = row pair, d4 = image
+    const int Hp = stem_Hp(g.H), Wp = stem_Wp(g.W);
+    const uint64_t rowpitch = uint64_t(Wp) * 4 * 2;
+    uint64_t dims[5] = {32, uint64_t(g.Wo), 2, uint64_t(Hp / 2), uint64_t(g.B)};
+    uint64_t str[4] = {16, rowpitch, 2 * rowpitch, uint64_t(Hp) * rowpitch};
+    uint32_t box[5] = {32, uint32_t(bw), 1, uint32_t(bh), uint32_t(bn)};
+    uint32_t es[5] = {1, 1, 1, 1, 1};
+    ok = encode(&pl->tmA, dt, 5, in, dims, str, box, es, true, msg);
+    if (ok) {
+      uint64_t wd[2] = {uint64_t(7 * 32), uint64_t(g.Cout)};
+      uint64_t ws[1] = {uint64_t(7 * 32) * 2};
+      uint32_t wb[2] = {32, uint32_t(pl->block_n)};
+      uint32_t we[2] = {1, 1};
+      ok = encode(&pl->tmW, dt, 2, w_packed, wd, ws, wb, we, true, msg);
+    }
+  } else {
+    ok = encode_act(&pl->tmA, dt, in, g.B, g.H, g.W, g.Cin, bw, bh, bn, g.stride, msg);
+    if (ok) {
+      const uint64_t K = uint64_t(g.kh) * g.kw * g.Cin;
+      uint64_t wd[2] = {K, uint64_t(g.Cout)};
+      uint64_t ws[1] = {K * 2};
+      uint32_t wb[2] = {64, uint32_t(pl->block_n)};
+      uint32_t we[2] = {1, 1};
+      ok = encode(&pl->tmW, dt, 2, w_packed, wd, ws, wb, we, false, msg);
+    }
+  }
+  // unused maps still need to be valid objects to pass by value: alias the output map
+  const void* any_out = e.out ? e.out : e.out_act;
+  if (ok) ok = encode_act(&pl->tmOut, dt, e.out ? e.out : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
+  if (ok) ok = encode_act(&pl->tmAct, dt, e.out_act ? e.out_act : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
+  if (ok) ok = encode_act(&pl->tmRes, dt, e.residual ? e.residual : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
+  if (!ok) { delete pl; return failmsg(msg); }
+  return pl;
+}
+
+void umma_conv_plan_destroy(UmmaConvPlan* p) { delete p; }
+
+cudaError_t umma_take_timeout_flag(unsigned int* flag) {
+  *flag = 0;
+  cudaError_t e = cudaMemcpyFromSymbol(flag, g_umma_timeout, sizeof(unsigned int));
+  if (e != cudaSuccess) return e;
+  if (*flag) {
+    unsigned int zero = 0;
+    e = cudaMemcpyToSymbol(g_umma_timeout, &zero, sizeof zero);
+  }
+  return e;
+}
+
+}  // namespace rn

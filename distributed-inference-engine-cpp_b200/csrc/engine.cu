@@ -1,0 +1,706 @@
+// Device runtime + C ABI (include/b200rn.h) of the B200 ResNet backend.
+//
+// One handle = one replica on one GPU: weights uploaded once, one activation arena laid out by
+// tensor liveness, three streams (H2D, compute, D2H) and two transfer slots so that batch i+1's
+// input crosses PCIe while batch i is being computed (the reference runs one batch at a time under
+// a mutex with a synchronous Session::Run, src/inference_engine.cpp:136,176-183).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/b200rn.h"
+#include "kernels.h"
+#include "onnx_reader.h"
+#include "plan.h"
+
+using namespace rn;
+
+namespace {
+
+thread_local std::string g_error;
+
+std::string fmt(const char* f, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, f);
+  vsnprintf(buf, sizeof buf, f, ap);
+  va_end(ap);
+  return buf;
+}
+
+struct CudaFail { std::string msg; };
+#define CK(expr)                                                                                       \
+  do {                                                                                                 \
+    cudaError_t _e = (expr);                                                                           \
+    if (_e != cudaSuccess) throw CudaFail{fmt("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__)}; \
+  } while (0)
+
+struct ArgFail { std::string msg; };
+
+inline int stem_Hp(int H) { return H + 6; }
+inline int stem_Wp(int W) { return ((W + 3 + 5) + 7) / 8 * 8; }
+
+struct DevLayer {
+  float* bias = nullptr;
+  float* act_scale = nullptr;
+  float* act_shift = nullptr;
+  void* w = nullptr;
+  bool umma = false;
+  int stem = 0;
+  std::map<int, UmmaConvPlan*> plans;   // per batch size
+  double weight_bytes = 0;
+};
+
+struct Slot {
+  float* d_in = nullptr;
+  float* d_out = nullptr;
+  float* h_in = nullptr;    // pinned staging for the ragged entry point
+  cudaEvent_t h2d_done = nullptr, fwd_done = nullptr, done = nullptr;
+  bool busy = false;
+};
+
+template <typename T>
+T* upload(const std::vector<T>& v) {
+  if (v.empty()) return nullptr;
+  T* d = nullptr;
+  CK(cudaMalloc(&d, v.size() * sizeof(T)));
+  CK(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return d;
+}
+
+}  // namespace
+
+struct b200rn {
+  int device = 0;
+  int mode = 0;
+  DType dt = DType::F32;
+  int max_batch = 256;
+  Plan plan;
+  std::vector<DevLayer> dl;
+  uint8_t* arena = nullptr;
+  size_t arena_bytes = 0;
+  std::vector<size_t> toff;       // byte offset of each tensor in the arena (sized for max_batch)
+  void* stem_frame = nullptr;     // zero-bordered [max_batch, Hp, Wp, 4] input frame (16-bit modes)
+  int stem_tensor = -1;
+  cudaStream_t s_h2d = nullptr, s_compute = nullptr, s_d2h = nullptr;
+  Slot slot[2];
+  mutable std::mutex mu;
+  mutable std::string err;
+  unsigned int* d_timeout_flag = nullptr;
+
+  ~b200rn() {
+    cudaSetDevice(device);
+    for (auto& L : dl) {
+      cudaFree(L.bias); cudaFree(L.act_scale); cudaFree(L.act_shift); cudaFree(L.w);
+      for (auto& kv : L.plans) umma_conv_plan_destroy(kv.second);
+    }
+    cudaFree(arena);
+    cudaFree(stem_frame);
+    for (auto& s : slot) {
+      cudaFree(s.d_in); cudaFree(s.d_out);
+      if (s.h_in) cudaFreeHost(s.h_in);
+      if (s.h2d_done) cudaEventDestroy(s.h2d_done);
+      if (s.fwd_done) cudaEventDestroy(s.fwd_done);
+      if (s.done) cudaEventDestroy(s.done);
+    }
+    if (s_h2d) cudaStreamDestroy(s_h2d);
+    if (s_compute) cudaStreamDestroy(s_compute);
+    if (s_d2h) cudaStreamDestroy(s_d2h);
+  }
+
+  size_t elsize(const PlanTensor& t) const { return t.vec_f32 ? 4 : dtype_size(dt); }
+
+  void* tptr(int t) const {
+    if (t < 0) return nullptr;
+    if (t == stem_tensor && stem_frame) return stem_frame;
+    return arena + toff[size_t(t)];
+  }
+
+  // ---- arena layout by liveness: first-fit over a free list, blocks aligned to 1 KB ----------
+  void layout_arena() {
+    struct Blk { size_t off, size; };
+    std::vector<Blk> free_list;
+    size_t top = 0;
+    toff.assign(plan.tensors.size(), 0);
+    auto alloc = [&](size_t bytes) {
+      bytes = (bytes + 1023) / 1024 * 1024;
+      for (size_t i = 0; i < free_list.size(); ++i)
+        if (free_list[i].size >= bytes) {
+          size_t off = free_list[i].off;
+          free_list[i].off += bytes;
+          free_list[i].size -= bytes;
+          if (!free_list[i].size) free_list.erase(free_list.begin() + long(i));
+          return off;
+        }
+      size_t off = top;
+      top += bytes;
+      return off;
+    };
+    auto release = [&](size_t off, size_t bytes) {
+      bytes = (bytes + 1023) / 1024 * 1024;
+      free_list.push_back({off, bytes});
+      std::sort(free_list.begin(), free_list.end(), [](const Blk& a, const Blk& b) { return a.off < b.off; });
+      for (size_t i = 0; i + 1 < free_list.size();)
+        if (free_list[i].off + free_list[i].size == free_list[i + 1].off) {
+          free_list[i].size += free_list[i + 1].size;
+          free_list.erase(free_list.begin() + long(i) + 1);
+        } else ++i;
+    };
+    auto bytes_of = [&](const PlanTensor& t) { return size_t(t.elems_per_sample()) * size_t(max_batch) * elsize(t); };
+    for (int li = 0; li < int(plan.layers.size()); ++li) {
+      for (auto& t : plan.tensors)
+        if (t.def_layer == li && t.id != stem_tensor) toff[size_t(t.id)] = alloc(bytes_of(t));
+      for (auto& t : plan.tensors)
+        if (t.def_layer >= 0 && t.last_use == li && t.id != stem_tensor && !t.is_output) release(toff[size_t(t.id)], bytes_of(t));
+    }
+    arena_bytes = std::max<size_t>(top, 1024);
+  }
+
+  void build(const std::string& path) {
+    OnnxModel model = load_onnx(path);
+    plan = build_plan(model, dt == DType::F32 ? 4 : 8);
+    CK(cudaSetDevice(device));
+    CK(cudaStreamCreateWithFlags(&s_h2d, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&s_compute, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&s_d2h, cudaStreamNonBlocking));
+    dl.resize(plan.layers.size());
+    for (size_t i = 0; i < plan.layers.size(); ++i) {
+      const PlanLayer& L = plan.layers[i];
+      DevLayer& D = dl[i];
+      D.bias = upload(L.bias);
+      D.act_scale = upload(L.act_scale);
+      D.act_shift = upload(L.act_shift);
+      if (L.kind == LayerKind::Conv || L.kind == LayerKind::Gemm) {
+        const bool fast_conv = L.kind == LayerKind::Conv && dt != DType::F32;
+        if (fast_conv) {
+          const PlanTensor& in = plan.tensors[size_t(L.in)];
+          ConvGeom g{1, in.H, in.W, L.Cin, 0, 0, L.Cout, L.kh, L.kw, L.stride, L.pad};
+          D.stem = (plan.layers[size_t(in.def_layer)].kind == LayerKind::InputXform && in.Cpad == 4) ? 1 : 0;
+          char why[256];
+          if (!umma_conv_supported(g, D.stem, why, sizeof why))
+            throw ArgFail{fmt("layer '%s' cannot run in a 16-bit tensor-core mode: %s (use B200RN_MODE_EXACT)", L.name.c_str(), why)};
+          D.umma = true;
+          size_t bytes = umma_weight_bytes(g, D.stem);
+          std::vector<uint8_t> packed(bytes);
+          umma_pack_weights(L.weight.data(), g, dt, D.stem, packed.data());
+          CK(cudaMalloc(&D.w, bytes));
+          CK(cudaMemcpy(D.w, packed.data(), bytes, cudaMemcpyHostToDevice));
+          D.weight_bytes = double(bytes);
+          if (D.stem) stem_tensor = L.in;
+        } else {
+          // fp32 CUDA-core path wants W^T: [K][Cout]
+          const int K = L.kind == LayerKind::Gemm ? L.Cin : L.kh * L.kw * L.Cin;
+          std::vector<float> wt(size_t(K) * L.Cout);
+          for (int o = 0; o < L.Cout; ++o)
+            for (int k = 0; k < K; ++k) wt[size_t(k) * L.Cout + o] = L.weight[size_t(o) * K + k];
+          D.w = upload(wt);
+          D.weight_bytes = double(wt.size()) * 4;
+        }
+      }
+    }
+    if (stem_tensor >= 0) {
+      const PlanTensor& t = plan.tensors[size_t(stem_tensor)];
+      size_t bytes = size_t(max_batch) * stem_Hp(t.H) * stem_Wp(t.W) * 4 * 2;
+      CK(cudaMalloc(&stem_frame, bytes));
+      CK(cudaMemset(stem_frame, 0, bytes));
+    }
+    layout_arena();
+    CK(cudaMalloc(&arena, arena_bytes));
+    for (auto& s : slot) {
+      CK(cudaMalloc(&s.d_in, size_t(max_batch) * size_t(plan.in_elems_per_sample) * 4));
+      CK(cudaMalloc(&s.d_out, size_t(max_batch) * size_t(plan.out_elems_per_sample) * 4));
+      CK(cudaEventCreateWithFlags(&s.h2d_done, cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&s.fwd_done, cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+    }
+    CK(cudaDeviceSynchronize());
+  }
+
+  ConvGeom geom(const PlanLayer& L, int B) const {
+    const PlanTensor& in = plan.tensors[size_t(L.in)];
+    const PlanTensor& out = plan.tensors[size_t(L.out >= 0 ? L.out : L.out_act)];
+    return ConvGeom{B, in.H, in.W, L.Cin, out.H, out.W, L.Cout, L.kh, L.kw, L.stride, L.pad};
+  }
+
+  // Launch layer li for a batch of B.  `d_in` feeds the InputXform, `d_out` receives the graph output.
+  void launch_layer(int li, int B, const float* d_in, float* d_out, cudaStream_t s) {
+    const PlanLayer& L = plan.layers[size_t(li)];
+    DevLayer& D = dl[size_t(li)];
+    auto out_ptr = [&](int t) -> void* {
+      if (t < 0) return nullptr;
+      return plan.tensors[size_t(t)].is_output ? static_cast<void*>(d_out) : tptr(t);
+    };
+    Epilogue e;
+    e.bias = D.bias; e.act_scale = D.act_scale; e.act_shift = D.act_shift;
+    e.relu = L.relu; e.act_relu = L.act_relu;
+    e.out = out_ptr(L.out); e.out_act = out_ptr(L.out_act);
+    switch (L.kind) {
+      case LayerKind::InputXform: {
+        const PlanTensor& t = plan.tensors[size_t(L.out)];
+        const bool framed = (L.out == stem_tensor && stem_frame);
+        CK(launch_input_xform(d_in, tptr(L.out), dt, B, t.C, t.H, t.W, t.Cpad, framed ? stem_Hp(t.H) : t.H,
+                              framed ? stem_Wp(t.W) : t.W, framed ? 3 : 0, framed ? 3 : 0, D.act_scale, D.act_shift,
+                              L.act_relu, s));
+        break;
+      }
+      case LayerKind::Conv: {
+        ConvGeom g = geom(L, B);
+        e.residual = tptr(L.in2);
+        if (D.umma) {
+          UmmaConvPlan*& up = D.plans[B];
+          if (!up) {
+            char msg[512] = {0};
+            up = umma_conv_plan_create(dt, g, tptr(L.in), D.w, e, D.stem, msg, sizeof msg);
+            if (!up) { D.plans.erase(B); throw CudaFail{fmt("layer '%s': %s", L.name.c_str(), msg)}; }
+          }
+          CK(launch_conv_umma(up, s));
+        } else {
+          CK(launch_conv_simt_f32(static_cast<const float*>(tptr(L.in)), static_cast<const float*>(D.w), g, e, s));
+        }
+        break;
+      }
+      case LayerKind::Gemm: {
+        // [B, K] x W^T[K][N] + bias on the fp32 CUDA-core kernel (a 1x1 conv over a 1x1 image)
+        ConvGeom g{B, 1, 1, L.Cin, 1, 1, L.Cout, 1, 1, 1, 0};
+        Epilogue ge;
+        ge.bias = D.bias; ge.out = out_ptr(L.out);
+        CK(launch_conv_simt_f32(static_cast<const float*>(tptr(L.in)), static_cast<const float*>(D.w), g, ge, s));
+        break;
+      }
+      case LayerKind::MaxPool: {
+        const PlanTensor& in = plan.tensors[size_t(L.in)];
+        const PlanTensor& out = plan.tensors[size_t(L.out >= 0 ? L.out : L.out_act)];
+        CK(launch_maxpool(tptr(L.in), dt, B, in.H, in.W, in.Cpad, out.H, out.W, L.pool_k, L.pool_stride, L.pool_pad, e, s));
+        break;
+      }
+      case LayerKind::Affine: {
+        const PlanTensor& in = plan.tensors[size_t(L.in)];
+        CK(launch_affine(tptr(L.in), tptr(L.out), dt, int64_t(B) * in.H * in.W, in.Cpad, D.act_scale, D.act_shift, L.act_relu, s));
+        break;
+      }
+      case LayerKind::Add: {
+        const PlanTensor& in = plan.tensors[size_t(L.in)];
+        if (in.vec_f32) throw ArgFail{"Add on flattened rows is not supported"};
+        CK(launch_add(tptr(L.in), tptr(L.in2), tptr(L.out), dt, int64_t(B) * in.elems_per_sample(), s));
+        break;
+      }
+      case LayerKind::Gap: {
+        const PlanTensor& in = plan.tensors[size_t(L.in)];
+        CK(launch_gap(tptr(L.in), dt, B, in.H * in.W, in.Cpad, in.C, D.act_scale, D.act_shift, L.act_relu,
+                      static_cast<float*>(out_ptr(L.out)), s));
+        break;
+      }
+      case LayerKind::Softmax: {
+        const PlanTensor& in = plan.tensors[size_t(L.in)];
+        CK(launch_softmax_rows(static_cast<const float*>(tptr(L.in)), static_cast<float*>(out_ptr(L.out)), B, in.C, s));
+        break;
+      }
+    }
+  }
+
+  void forward(int B, const float* d_in, float* d_out, cudaStream_t s) {
+    for (int li = 0; li < int(plan.layers.size()); ++li) launch_layer(li, B, d_in, d_out, s);
+  }
+
+  void check_batch(size_t batch) const {
+    if (batch > size_t(max_batch)) throw ArgFail{fmt("batch %zu exceeds max_batch %d of this handle", batch, max_batch)};
+  }
+
+  void submit(int si, const float* nchw, size_t batch, float* out) {
+    Slot& s = slot[si];
+    if (s.busy) throw ArgFail{"slot is busy: call b200rn_wait first"};
+    check_batch(batch);
+    const size_t in_bytes = batch * size_t(plan.in_elems_per_sample) * 4;
+    const size_t out_bytes = batch * size_t(plan.out_elems_per_sample) * 4;
+    CK(cudaMemcpyAsync(s.d_in, nchw, in_bytes, cudaMemcpyHostToDevice, s_h2d));
+    CK(cudaEventRecord(s.h2d_done, s_h2d));
+    CK(cudaStreamWaitEvent(s_compute, s.h2d_done, 0));
+    forward(int(batch), s.d_in, s.d_out, s_compute);
+    CK(cudaEventRecord(s.fwd_done, s_compute));
+    CK(cudaStreamWaitEvent(s_d2h, s.fwd_done, 0));
+    CK(cudaMemcpyAsync(out, s.d_out, out_bytes, cudaMemcpyDeviceToHost, s_d2h));
+    CK(cudaEventRecord(s.done, s_d2h));
+    s.busy = true;
+  }
+
+  void check_kernel_health() {
+    if (dt == DType::F32) return;
+    unsigned int flag = 0;
+    CK(umma_take_timeout_flag(&flag));
+    if (flag) throw CudaFail{"a tensor-core conv kernel gave up waiting on a TMA/MMA barrier; results are invalid"};
+  }
+
+  void wait(int si) {
+    Slot& s = slot[si];
+    if (!s.busy) throw ArgFail{"wait on an idle slot"};
+    s.busy = false;
+    CK(cudaEventSynchronize(s.done));
+    check_kernel_health();
+  }
+
+  // whole batch in slices of max_batch, alternating slots so transfers overlap compute
+  void run_packed(const float* nchw, size_t batch, float* out) {
+    const size_t ie = size_t(plan.in_elems_per_sample), oe = size_t(plan.out_elems_per_sample);
+    size_t done = 0;
+    int si = 0;
+    bool pending[2] = {false, false};
+    while (done < batch) {
+      size_t n = std::min(batch - done, size_t(max_batch));
+      if (pending[si]) { wait(si); pending[si] = false; }
+      submit(si, nchw + done * ie, n, out + done * oe);
+      pending[si] = true;
+      done += n;
+      si ^= 1;
+    }
+    for (int k = 0; k < 2; ++k)
+      if (pending[k]) wait(k);
+  }
+};
+
+namespace {
+
+template <typename F>
+int guarded(const b200rn_t* h, F&& f) {
+  std::string* err = h ? &h->err : &g_error;
+  try {
+    f();
+    return B200RN_OK;
+  } catch (const CudaFail& e) { *err = e.msg; return B200RN_ERR_CUDA; }
+  catch (const ArgFail& e) { *err = e.msg; return B200RN_ERR_ARG; }
+  catch (const std::exception& e) { *err = e.what(); return B200RN_ERR_MODEL; }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* b200rn_global_error(void) { return g_error.c_str(); }
+const char* b200rn_last_error(const b200rn_t* h) { return h ? h->err.c_str() : g_error.c_str(); }
+
+int b200rn_create(const char* onnx_path, int device, int mode, int max_batch, b200rn_t** out) {
+  if (!onnx_path || !out) { g_error = "b200rn_create: null argument"; return B200RN_ERR_ARG; }
+  if (mode < 0 || mode > 2) { g_error = "b200rn_create: unknown mode"; return B200RN_ERR_ARG; }
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev == 0) {
+    // no CPU fallback: the product path is the GPU path
+    g_error = std::string("b200rn_create: no CUDA device available (") + cudaGetErrorString(ce) + "); this backend has no CPU path";
+    return B200RN_ERR_CUDA;
+  }
+  if (device < 0 || device >= ndev) { g_error = fmt("b200rn_create: device %d out of range (%d present)", device, ndev); return B200RN_ERR_ARG; }
+  std::unique_ptr<b200rn> h(new b200rn());
+  h->device = device;
+  h->mode = mode;
+  h->dt = mode == B200RN_MODE_EXACT ? DType::F32 : (mode == B200RN_MODE_BF16 ? DType::BF16 : DType::F16);
+  h->max_batch = max_batch > 0 ? max_batch : 256;
+  int rc = guarded(nullptr, [&] { h->build(onnx_path); });
+  if (rc != B200RN_OK) return rc;
+  *out = h.release();
+  return B200RN_OK;
+}
+
+void b200rn_destroy(b200rn_t* h) { delete h; }
+
+static int copy_shape(const std::vector<int64_t>& s, int64_t* dims, int cap) {
+  for (int i = 0; i < int(s.size()) && i < cap; ++i) dims[i] = s[size_t(i)];
+  return int(s.size());
+}
+int b200rn_input_shape(const b200rn_t* h, int64_t* dims, int cap) { return h ? copy_shape(h->plan.input_shape, dims, cap) : -1; }
+int b200rn_output_shape(const b200rn_t* h, int64_t* dims, int cap) { return h ? copy_shape(h->plan.output_shape, dims, cap) : -1; }
+int64_t b200rn_input_elems(const b200rn_t* h) { return h ? h->plan.in_elems_per_sample : -1; }
+int64_t b200rn_output_elems(const b200rn_t* h) { return h ? h->plan.out_elems_per_sample : -1; }
+
+int b200rn_infer_packed(b200rn_t* h, const float* nchw, size_t batch, float* out) {
+  if (!h) { g_error = "null handle"; return B200RN_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(h->mu);
+  if (batch == 0) return B200RN_OK;
+  if (!nchw || !out) { h->err = "b200rn_infer_packed: null buffer"; return B200RN_ERR_ARG; }
+  return guarded(h, [&] { CK(cudaSetDevice(h->device)); h->run_packed(nchw, batch, out); });
+}
+
+int b200rn_infer(b200rn_t* h, const float* const* samples, const size_t* sample_len, size_t batch, float* out) {
+  if (!h) { g_error = "null handle"; return B200RN_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(h->mu);
+  if (batch == 0) return B200RN_OK;   // reference: empty batch -> {} (src/inference_engine.cpp:137-139)
+  if (!samples || !sample_len || !out) { h->err = "b200rn_infer: null argument"; return B200RN_ERR_ARG; }
+  const size_t ie = size_t(h->plan.in_elems_per_sample), oe = size_t(h->plan.out_elems_per_sample);
+  for (size_t i = 0; i < batch; ++i) {
+    if (!samples[i] && sample_len[i]) { h->err = fmt("b200rn_infer: sample %zu is null", i); return B200RN_ERR_ARG; }
+    if (sample_len[i] > ie) {
+      h->err = fmt("b200rn_infer: sample %zu has %zu values, the model input holds %zu", i, sample_len[i], ie);
+      return B200RN_ERR_ARG;
+    }
+  }
+  return guarded(h, [&] {
+    CK(cudaSetDevice(h->device));
+    // pack (zero-padded) straight into pinned staging, slice by slice, alternating slots
+    size_t done = 0;
+    int si = 0;
+    bool pending[2] = {false, false};
+    while (done < batch) {
+      size_t n = std::min(batch - done, size_t(h->max_batch));
+      Slot& s = h->slot[si];
+      if (pending[si]) { h->wait(si); pending[si] = false; }
+      if (!s.h_in) CK(cudaMallocHost(&s.h_in, size_t(h->max_batch) * ie * 4));
+      for (size_t i = 0; i < n; ++i) {
+        float* dst = s.h_in + i * ie;
+        size_t len = sample_len[done + i];
+        if (len) std::memcpy(dst, samples[done + i], len * 4);
+        if (len < ie) std::memset(dst + len, 0, (ie - len) * 4);
+      }
+      h->submit(si, s.h_in, n, out + done * oe);
+      pending[si] = true;
+      done += n;
+      si ^= 1;
+    }
+    for (int k = 0; k < 2; ++k)
+      if (pending[k]) h->wait(k);
+  });
+}
+
+int b200rn_predict(b200rn_t* h, const float* sample, size_t len, float* out) {
+  if (!h) { g_error = "null handle"; return B200RN_ERR_ARG; }
+  // pad AND truncate (src/inference_engine.cpp:100-103)
+  size_t ie = size_t(h->plan.in_elems_per_sample);
+  size_t n = std::min(len, ie);
+  const float* one[1] = {sample};
+  size_t lens[1] = {n};
+  return b200rn_infer(h, one, lens, 1, out);
+}
+
+int b200rn_infer_device(b200rn_t* h, const float* d_nchw, size_t batch, float* d_out) {
+  if (!h) { g_error = "null handle"; return B200RN_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(h->mu);
+  if (batch == 0) return B200RN_OK;
+  return guarded(h, [&] {
+    CK(cudaSetDevice(h->device));
+    const size_t ie = size_t(h->plan.in_elems_per_sample), oe = size_t(h->plan.out_elems_per_sample);
+    for (size_t done = 0; done < batch;) {
+      size_t n = std::min(batch - done, size_t(h->max_batch));
+      h->forward(int(n), d_nchw + done * ie, d_out + done * oe, h->s_compute);
+      done += n;
+    }
+    CK(cudaStreamSynchronize(h->s_compute));
+    h->check_kernel_health();
+  });
+}
+
+int b200rn_submit_packed(b200rn_t* h, int slot, const float* nchw, size_t batch, float* out) {
+  if (!h) { g_error = "null handle"; return B200RN_ERR_ARG; }
+  if (slot < 0 || slot > 1 || !nchw || !out || batch == 0) { h->err = "b200rn_submit_packed: bad argument"; return B200RN_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(h->mu);
+  int rc = guarded(h, [&] { CK(cudaSetDevice(h->device)); h->submit(slot, nchw, batch, out); });
+  return rc;
+}
+
+int b200rn_wait(b200rn_t* h, int slot) {
+  if (!h) { g_error = "null handle"; return B200RN_ERR_ARG; }
+  if (slot < 0 || slot > 1) { h->err = "b200rn_wait: bad slot"; return B200RN_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(h->mu);
+  if (!h->slot[slot].busy) { h->err = "b200rn_wait: slot has no submitted batch"; return B200RN_ERR_STATE; }
+  return guarded(h, [&] { CK(cudaSetDevice(h->device)); h->wait(slot); });
+}
+
+void* b200rn_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaMallocHost(&p, bytes) != cudaSuccess) { g_error = "cudaMallocHost failed"; return nullptr; }
+  return p;
+}
+void b200rn_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int64_t b200rn_describe_plan(const char* onnx_path, int mode, char* buf, size_t cap) {
+  std::string text;
+  int rc = guarded(nullptr, [&] {
+    OnnxModel m = load_onnx(onnx_path);
+    Plan p = build_plan(m, mode == B200RN_MODE_EXACT ? 4 : 8);
+    text = p.describe();
+  });
+  if (rc != B200RN_OK) return -1;
+  if (buf && cap) {
+    size_t n = std::min(cap - 1, text.size());
+    std::memcpy(buf, text.data(), n);
+    buf[n] = 0;
+  }
+  return int64_t(text.size());
+}
+
+int b200rn_layer_count(const b200rn_t* h) { return h ? int(h->plan.layers.size()) : -1; }
+int b200rn_launch_count(const b200rn_t* h) { return h ? int(h->plan.layers.size()) : -1; }
+
+int b200rn_layer_name(const b200rn_t* h, int i, char* buf, size_t cap) {
+  if (!h || i < 0 || i >= int(h->plan.layers.size()) || !buf || !cap) return B200RN_ERR_ARG;
+  std::snprintf(buf, cap, "%s", h->plan.layers[size_t(i)].name.c_str());
+  return B200RN_OK;
+}
+
+int b200rn_profile_layers(b200rn_t* h, const float* d_nchw, size_t batch, int iters, float* ms, int* kinds,
+                          double* flops, double* bytes) {
+  if (!h || !d_nchw || !ms || batch == 0 || iters <= 0) { g_error = "b200rn_profile_layers: bad argument"; return B200RN_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(h->mu);
+  return guarded(h, [&] {
+    CK(cudaSetDevice(h->device));
+    h->check_batch(batch);
+    const int nl = int(h->plan.layers.size());
+    std::vector<cudaEvent_t> ev(size_t(nl) + 1);
+    for (auto& e : ev) CK(cudaEventCreate(&e));
+    std::vector<double> acc(size_t(nl), 0.0);
+    float* d_out = h->slot[0].d_out;
+    h->forward(int(batch), d_nchw, d_out, h->s_compute);   // warm-up (also builds the TMA descriptors)
+    CK(cudaStreamSynchronize(h->s_compute));
+    for (int it = 0; it < iters; ++it) {
+      CK(cudaEventRecord(ev[0], h->s_compute));
+      for (int li = 0; li < nl; ++li) {
+        h->launch_layer(li, int(batch), d_nchw, d_out, h->s_compute);
+        CK(cudaEventRecord(ev[size_t(li) + 1], h->s_compute));
+      }
+      CK(cudaStreamSynchronize(h->s_compute));
+      for (int li = 0; li < nl; ++li) {
+        float t = 0;
+        CK(cudaEventElapsedTime(&t, ev[size_t(li)], ev[size_t(li) + 1]));
+        acc[size_t(li)] += t;
+      }
+    }
+    for (auto& e : ev) cudaEventDestroy(e);
+    for (int li = 0; li < nl; ++li) {
+      const PlanLayer& L = h->plan.layers[size_t(li)];
+      ms[li] = float(acc[size_t(li)] / iters);
+      if (kinds) kinds[li] = int(L.kind);
+      if (flops) flops[li] = 2.0 * L.macs_per_sample * double(batch);
+      if (bytes) {
+        double b = h->dl[size_t(li)].weight_bytes;
+        for (int t : {L.in, L.in2, L.out, L.out_act})
+          if (t >= 0) {
+            const PlanTensor& T = h->plan.tensors[size_t(t)];
+            b += double(T.elems_per_sample()) * double(batch) * double(h->elsize(T));
+          }
+        if (L.kind == LayerKind::InputXform) b += double(h->plan.in_elems_per_sample) * 4.0 * double(batch);
+        bytes[li] = b;
+      }
+    }
+  });
+}
+
+int b200rn_time_forward(b200rn_t* h, const float* d_nchw, size_t batch, int iters, float* ms_total) {
+  if (!h || !d_nchw || !ms_total || batch == 0 || iters <= 0) { g_error = "b200rn_time_forward: bad argument"; return B200RN_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(h->mu);
+  return guarded(h, [&] {
+    CK(cudaSetDevice(h->device));
+    h->check_batch(batch);
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a));
+    CK(cudaEventCreate(&b));
+    CK(cudaStreamSynchronize(h->s_compute));
+    CK(cudaEventRecord(a, h->s_compute));
+    for (int i = 0; i < iters; ++i) h->forward(int(batch), d_nchw, h->slot[0].d_out, h->s_compute);
+    CK(cudaEventRecord(b, h->s_compute));
+    CK(cudaEventSynchronize(b));
+    CK(cudaEventElapsedTime(ms_total, a, b));
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+  });
+}
+
+// ---- single-operator entry points ---------------------------------------------------------------
+
+int b200rn_conv2d(int dtype, const void* d_in, int B, int H, int W, int Cin, const float* w, const float* bias,
+                  int Cout, int kh, int kw, int stride, int pad, int relu, const void* d_residual, void* d_out,
+                  void* d_out_act, const float* act_scale, const float* act_shift, int act_relu) {
+  if (!d_in || !w || (!d_out && !d_out_act) || dtype < 0 || dtype > 2) { g_error = "b200rn_conv2d: bad argument"; return B200RN_ERR_ARG; }
+  return guarded(nullptr, [&] {
+    DType dt = DType(dtype);
+    const int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+    ConvGeom g{B, H, W, Cin, Ho, Wo, Cout, kh, kw, stride, pad};
+    std::vector<float> zeros(size_t(Cout), 0.f), ones(size_t(Cout), 1.f);
+    std::vector<float> hb(bias ? bias : zeros.data(), (bias ? bias : zeros.data()) + Cout);
+    std::vector<float> hs(act_scale ? act_scale : ones.data(), (act_scale ? act_scale : ones.data()) + Cout);
+    std::vector<float> ht(act_shift ? act_shift : zeros.data(), (act_shift ? act_shift : zeros.data()) + Cout);
+    float* db = upload(hb); float* ds = upload(hs); float* dsh = upload(ht);
+    Epilogue e;
+    e.bias = db; e.act_scale = ds; e.act_shift = dsh; e.relu = relu; e.act_relu = act_relu;
+    e.residual = d_residual; e.out = d_out; e.out_act = d_out_act;
+    void* dw = nullptr;
+    if (dt == DType::F32) {
+      const int K = kh * kw * Cin;
+      std::vector<float> wt(size_t(K) * Cout);
+      for (int o = 0; o < Cout; ++o)
+        for (int k = 0; k < K; ++k) wt[size_t(k) * Cout + o] = w[size_t(o) * K + k];
+      dw = upload(wt);
+      CK(launch_conv_simt_f32(static_cast<const float*>(d_in), static_cast<const float*>(dw), g, e, 0));
+      CK(cudaDeviceSynchronize());
+    } else {
+      size_t bytes = umma_weight_bytes(g, 0);
+      std::vector<uint8_t> packed(bytes);
+      umma_pack_weights(w, g, dt, 0, packed.data());
+      CK(cudaMalloc(&dw, bytes));
+      CK(cudaMemcpy(dw, packed.data(), bytes, cudaMemcpyHostToDevice));
+      char msg[512] = {0};
+      UmmaConvPlan* up = umma_conv_plan_create(dt, g, d_in, dw, e, 0, msg, sizeof msg);
+      if (!up) { cudaFree(dw); cudaFree(db); cudaFree(ds); cudaFree(dsh); throw CudaFail{std::string("b200rn_conv2d: ") + msg}; }
+      cudaError_t le = launch_conv_umma(up, 0);
+      cudaError_t se = cudaDeviceSynchronize();
+      umma_conv_plan_destroy(up);
+      unsigned int flag = 0;
+      if (se == cudaSuccess) se = umma_take_timeout_flag(&flag);
+      if (le != cudaSuccess || se != cudaSuccess || flag) {
+        cudaFree(dw); cudaFree(db); cudaFree(ds); cudaFree(dsh);
+        throw CudaFail{fmt("b200rn_conv2d: launch %s / sync %s / barrier timeout %u", cudaGetErrorString(le), cudaGetErrorString(se), flag)};
+      }
+    }
+    cudaFree(dw); cudaFree(db); cudaFree(ds); cudaFree(dsh);
+  });
+}
+
+int b200rn_stem_conv(int dtype, const float* d_in_nchw, int B, int H, int W, const float* in_scale,
+                     const float* in_shift, const float* w, const float* bias, int Cout, int relu, void* d_out) {
+  if (!d_in_nchw || !w || !d_out || dtype < 1 || dtype > 2) { g_error = "b200rn_stem_conv: bad argument"; return B200RN_ERR_ARG; }
+  return guarded(nullptr, [&] {
+    DType dt = DType(dtype);
+    const int Hp = stem_Hp(H), Wp = stem_Wp(W);
+    const int Ho = (H + 6 - 7) / 2 + 1, Wo = (W + 6 - 7) / 2 + 1;
+    ConvGeom g{B, H, W, 4, Ho, Wo, Cout, 7, 7, 2, 3};
+    std::vector<float> s4(4, 0.f), t4(4, 0.f);
+    for (int c = 0; c < 3; ++c) { s4[size_t(c)] = in_scale ? in_scale[c] : 1.f; t4[size_t(c)] = in_shift ? in_shift[c] : 0.f; }
+    float* ds = upload(s4); float* dsh = upload(t4);
+    std::vector<float> zeros(size_t(Cout), 0.f);
+    std::vector<float> hb(bias ? bias : zeros.data(), (bias ? bias : zeros.data()) + Cout);
+    float* db = upload(hb);
+    void* frame = nullptr;
+    size_t fbytes = size_t(B) * Hp * Wp * 4 * 2;
+    CK(cudaMalloc(&frame, fbytes));
+    CK(cudaMemset(frame, 0, fbytes));
+    CK(launch_input_xform(d_in_nchw, frame, dt, B, 3, H, W, 4, Hp, Wp, 3, 3, ds, dsh, 0, 0));
+    size_t bytes = umma_weight_bytes(g, 1);
+    std::vector<uint8_t> packed(bytes);
+    umma_pack_weights(w, g, dt, 1, packed.data());
+    void* dw = nullptr;
+    CK(cudaMalloc(&dw, bytes));
+    CK(cudaMemcpy(dw, packed.data(), bytes, cudaMemcpyHostToDevice));
+    Epilogue e;
+    e.bias = db; e.relu = relu; e.out = d_out;
+    char msg[512] = {0};
+    UmmaConvPlan* up = umma_conv_plan_create(dt, g, frame, dw, e, 1, msg, sizeof msg);
+    cudaError_t le = cudaSuccess, se = cudaSuccess;
+    unsigned int flag = 0;
+    if (up) {
+      le = launch_conv_umma(up, 0);
+      se = cudaDeviceSynchronize();
+      umma_conv_plan_destroy(up);
+      if (se == cudaSuccess) se = umma_take_timeout_flag(&flag);
+    }
+    cudaFree(frame); cudaFree(dw); cudaFree(db); cudaFree(ds); cudaFree(dsh);
+    if (!up) throw CudaFail{std::string("b200rn_stem_conv: ") + msg};
+    if (le != cudaSuccess || se != cudaSuccess || flag)
+      throw CudaFail{fmt("b200rn_stem_conv: launch %s / sync %s / barrier timeout %u", cudaGetErrorString(le), cudaGetErrorString(se), flag)};
+  });
+}
+
+}  // extern "C"

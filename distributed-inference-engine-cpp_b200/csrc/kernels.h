@@ -1,0 +1,76 @@
+// Launch interface of the sm_100a kernels (host side).  Activations are NHWC; element type is
+// float (exact mode) or bf16 / fp16 (tensor-core modes).  All launchers are asynchronous on the
+// given stream and return the cudaError_t of the launch.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+
+namespace rn {
+
+enum class DType : int { F32 = 0, BF16 = 1, F16 = 2 };
+inline size_t dtype_size(DType t) { return t == DType::F32 ? 4 : 2; }
+
+// Fused epilogue shared by both conv kernels and (partly) max-pool:
+//   v = acc + bias[c];  if (relu) v = max(v, 0);  if (residual) v += residual[m][c];
+//   if (out)     out[m][c]     = v;
+//   if (out_act) out_act[m][c] = act_relu ? max(act_scale[c]*v + act_shift[c], 0) : act_scale[c]*v + act_shift[c];
+struct Epilogue {
+  const float* bias = nullptr;
+  const void* residual = nullptr;
+  void* out = nullptr;
+  void* out_act = nullptr;
+  const float* act_scale = nullptr;
+  const float* act_shift = nullptr;
+  int relu = 0;
+  int act_relu = 0;
+};
+
+struct ConvGeom {
+  int B, H, W, Cin;        // input NHWC (Cin as stored)
+  int Ho, Wo, Cout;        // output NHWC (Cout as stored)
+  int kh, kw, stride, pad;
+};
+
+// NCHW fp32 [B,C,H,W] -> NHWC (C padded to Cpad with zeros), y = relu?(scale[c]*x + shift[c]).
+// The destination may be a spatially padded frame [B,Hp,Wp,Cpad] with the image at (off_h, off_w);
+// only the interior is written (borders are zeroed once at allocation).
+cudaError_t launch_input_xform(const float* nchw, void* out, DType dt, int B, int C, int H, int W, int Cpad,
+                               int Hp, int Wp, int off_h, int off_w, const float* scale, const float* shift,
+                               int relu, cudaStream_t s);
+
+// fp32 implicit-GEMM convolution on CUDA cores (exact mode, and the tiny FC in every mode).
+// w: [K = kh*kw*Cin][Cout] fp32.
+cudaError_t launch_conv_simt_f32(const float* in, const float* w, const ConvGeom& g, const Epilogue& e, cudaStream_t s);
+
+// max-pool k x k / stride / pad (padding excluded from the max), NHWC, with optional second output.
+cudaError_t launch_maxpool(const void* in, DType dt, int B, int H, int W, int C, int Ho, int Wo, int k, int stride,
+                           int pad, const Epilogue& e, cudaStream_t s);
+
+// out[b][c] = mean over H*W of relu?(scale[c]*x + shift[c]);  fp32 rows [B, Ctrue]; C = stored channels
+cudaError_t launch_gap(const void* in, DType dt, int B, int HW, int C, int Ctrue, const float* scale,
+                       const float* shift, int relu, float* out, cudaStream_t s);
+
+// stand-alone element-wise fallbacks (only used when the graph does not match a fusion)
+cudaError_t launch_affine(const void* in, void* out, DType dt, int64_t pixels, int C, const float* scale,
+                          const float* shift, int relu, cudaStream_t s);
+cudaError_t launch_add(const void* a, const void* b, void* out, DType dt, int64_t elems, cudaStream_t s);
+
+cudaError_t launch_softmax_rows(const float* in, float* out, int B, int N, cudaStream_t s);
+
+// ---- tensor-core path (conv_umma.cu) -------------------------------------------------------
+struct UmmaConvPlan;  // opaque: TMA descriptors + tile geometry for one conv layer at one batch size
+UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in, const void* w_packed,
+                                    const Epilogue& e, int stem_mode, char* err, size_t errcap);
+void umma_conv_plan_destroy(UmmaConvPlan*);
+cudaError_t launch_conv_umma(const UmmaConvPlan* p, cudaStream_t s);
+// bytes of the packed weight buffer and the host-side packer ([Cout][kh][kw][Cin] fp32 -> kernel layout)
+size_t umma_weight_bytes(const ConvGeom& g, int stem_mode);
+void umma_pack_weights(const float* w, const ConvGeom& g, DType dt, int stem_mode, void* dst);
+// Reads (and clears) the device flag a tensor-core conv sets when one of its barrier waits gave up.
+// Call after synchronising; a set flag means the results of that launch are invalid.
+cudaError_t umma_take_timeout_flag(unsigned int* flag);
+bool umma_conv_supported(const ConvGeom& g, int stem_mode, char* why, size_t cap);
+
+}  // namespace rn

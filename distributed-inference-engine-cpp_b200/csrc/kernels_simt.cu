@@ -1,0 +1,443 @@
+// CUDA-core kernels of the B200 ResNet backend: layout transform, fp32 implicit-GEMM conv (exact
+// mode + FC), max-pool, global average pool, element-wise fallbacks, softmax.
+// All memory-bound kernels use 16-byte vector accesses with consecutive threads on consecutive
+// channel vectors (NHWC => fully coalesced) and grids of at least a few waves over 148 SMs.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "kernels.h"
+
+namespace rn {
+namespace {
+
+constexpr int kSMs = 148;
+
+// ---- 16-byte vectors of T <-> float -------------------------------------------------------
+template <typename T> struct Vec;
+template <> struct Vec<float> {
+  static constexpr int N = 4;
+  __device__ static void load(const float* p, float (&v)[4]) {
+    float4 x = *reinterpret_cast<const float4*>(p);
+    v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
+  }
+  __device__ static void store(float* p, const float (&v)[4]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+  __device__ static float lowest() { return -3.402823466e+38f; }
+};
+template <> struct Vec<__nv_bfloat16> {
+  static constexpr int N = 8;
+  __device__ static void load(const __nv_bfloat16* p, float (&v)[8]) {
+    uint4 x = *reinterpret_cast<const uint4*>(p);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&x);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { float2 f = __bfloat1622float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+  }
+  __device__ static void store(__nv_bfloat16* p, const float (&v)[8]) {
+    uint4 x;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&x);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = x;
+  }
+};
+template <> struct Vec<__half> {
+  static constexpr int N = 8;
+  __device__ static void load(const __half* p, float (&v)[8]) {
+    uint4 x = *reinterpret_cast<const uint4*>(p);
+    const __half2* h = reinterpret_cast<const __half2*>(&x);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { float2 f = __half22float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+  }
+  __device__ static void store(__half* p, const float (&v)[8]) {
+    uint4 x;
+    __half2* h = reinterpret_cast<__half2*>(&x);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = x;
+  }
+};
+
+template <typename T> __device__ inline T from_float(float f);
+template <> __device__ inline float from_float<float>(float f) { return f; }
+template <> __device__ inline __nv_bfloat16 from_float<__nv_bfloat16>(float f) { return __float2bfloat16_rn(f); }
+template <> __device__ inline __half from_float<__half>(float f) { return __float2half_rn(f); }
+
+inline int grid_for(int64_t threads, int block) {
+  int64_t g = (threads + block - 1) / block;
+  if (g < 1) g = 1;
+  return int(g);
+}
+
+// ---- input re-layout ------------------------------------------------------------------------
+// One thread per pixel: reads C planes (coalesced along W), writes Cpad contiguous channels.
+template <typename T>
+__global__ void input_xform_kernel(const float* __restrict__ in, T* __restrict__ out, int B, int C, int H, int W,
+                                   int Cpad, int Hp, int Wp, int off_h, int off_w, const float* __restrict__ scale,
+                                   const float* __restrict__ shift, int relu) {
+  int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  int64_t total = int64_t(B) * H * W;
+  if (idx >= total) return;
+  int w = int(idx % W);
+  int h = int((idx / W) % H);
+  int b = int(idx / (int64_t(W) * H));
+  const float* src = in + (int64_t(b) * C * H + h) * W + w;
+  T* dst = out + ((int64_t(b) * Hp + h + off_h) * Wp + (w + off_w)) * Cpad;
+  for (int c = 0; c < Cpad; ++c) {
+    float v = 0.f;
+    if (c < C) {
+      v = fmaf(__ldg(scale + c), __ldg(src + int64_t(c) * H * W), __ldg(shift + c));
+      if (relu) v = fmaxf(v, 0.f);
+    }
+    dst[c] = from_float<T>(v);
+  }
+}
+
+// ---- fp32 implicit-GEMM conv ----------------------------------------------------------------
+// C[M = B*Ho*Wo][N = Cout] = A[M][K] * Wt[K][N], K ordered (ky, kx, cin).  128x64 CTA tile,
+// BK = 16, 256 threads, 8x4 register tile, double-buffered shared memory, global->register
+// prefetch of the next K slice during the FMAs.  A is gathered straight from the NHWC input in
+// float4 granules (4 consecutive channels of one tap), zero for padding taps.
+constexpr int BM = 128, BN = 64, BK = 16, SIMT_THREADS = 256;
+
+struct SimtConvParams {
+  const float* in; const float* w;
+  Epilogue e;
+  ConvGeom g;
+  int M, K;
+};
+
+__global__ void __launch_bounds__(SIMT_THREADS) conv_simt_f32_kernel(SimtConvParams p) {
+  __shared__ __align__(16) float As[2][BK][BM + 4];
+  __shared__ __align__(16) float Bs[2][BK][BN];
+  const ConvGeom& g = p.g;
+  const int tid = threadIdx.x;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+
+  // A-load role: row ar (0..127), 8 consecutive k starting at ak
+  const int ar = tid >> 1, ak = (tid & 1) * 8;
+  const int am = m0 + ar;
+  const bool a_row_ok = am < p.M;
+  int ih0 = 0, iw0 = 0;
+  const float* a_img = p.in;
+  if (a_row_ok) {
+    int wo = am % g.Wo, t = am / g.Wo;
+    int ho = t % g.Ho, b = t / g.Ho;
+    ih0 = ho * g.stride - g.pad;
+    iw0 = wo * g.stride - g.pad;
+    a_img = p.in + int64_t(b) * g.H * g.W * g.Cin;
+  }
+  // B-load role: k row bk (0..15), 4 consecutive n starting at bn
+  const int bk = tid >> 4, bn = (tid & 15) * 4;
+  const bool b_col_ok = (n0 + bn) < g.Cout;
+
+  float4 ra[2], rb;
+  auto load_global = [&](int k0) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      int k = k0 + ak + j * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (a_row_ok && k < p.K) {
+        int tap = k / g.Cin, c = k - tap * g.Cin;
+        int ky = tap / g.kw, kx = tap - ky * g.kw;
+        int ih = ih0 + ky, iw = iw0 + kx;
+        if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W)
+          v = __ldg(reinterpret_cast<const float4*>(a_img + (int64_t(ih) * g.W + iw) * g.Cin + c));
+      }
+      ra[j] = v;
+    }
+    int k = k0 + bk;
+    rb = (b_col_ok && k < p.K) ? __ldg(reinterpret_cast<const float4*>(p.w + int64_t(k) * g.Cout + n0 + bn))
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+  };
+  auto store_smem = [&](int buf) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      As[buf][ak + j * 4 + 0][ar] = ra[j].x;
+      As[buf][ak + j * 4 + 1][ar] = ra[j].y;
+      As[buf][ak + j * 4 + 2][ar] = ra[j].z;
+      As[buf][ak + j * 4 + 3][ar] = ra[j].w;
+    }
+    *reinterpret_cast<float4*>(&Bs[buf][bk][bn]) = rb;
+  };
+
+  const int ty = tid >> 4, tx = tid & 15;  // 16 x 16 threads, 8 rows x 4 cols each
+  float acc[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  const int KT = (p.K + BK - 1) / BK;
+  load_global(0);
+  store_smem(0);
+  __syncthreads();
+  for (int kt = 0; kt < KT; ++kt) {
+    const int buf = kt & 1;
+    if (kt + 1 < KT) load_global((kt + 1) * BK);
+#pragma unroll
+    for (int k = 0; k < BK; ++k) {
+      float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8]);
+      float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8 + 4]);
+      float4 b = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
+      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
+    }
+    if (kt + 1 < KT) store_smem(buf ^ 1);
+    __syncthreads();
+  }
+
+  // fused epilogue
+  const int n = n0 + tx * 4;
+  if (n >= g.Cout) return;
+  const Epilogue& e = p.e;
+  const float4 bias = __ldg(reinterpret_cast<const float4*>(e.bias + n));
+  float4 sc = make_float4(1.f, 1.f, 1.f, 1.f), sh = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (e.out_act) {
+    sc = __ldg(reinterpret_cast<const float4*>(e.act_scale + n));
+    sh = __ldg(reinterpret_cast<const float4*>(e.act_shift + n));
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    int m = m0 + ty * 8 + i;
+    if (m >= p.M) break;
+    int64_t off = int64_t(m) * g.Cout + n;
+    float4 v = make_float4(acc[i][0] + bias.x, acc[i][1] + bias.y, acc[i][2] + bias.z, acc[i][3] + bias.w);
+    if (e.relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+    if (e.residual) {
+      float4 r = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(e.residual) + off));
+      v.x += r.x; v.y += r.y; v.z += r.z; v.w += r.w;
+    }
+    if (e.out) *reinterpret_cast<float4*>(static_cast<float*>(e.out) + off) = v;
+    if (e.out_act) {
+      float4 a = make_float4(fmaf(sc.x, v.x, sh.x), fmaf(sc.y, v.y, sh.y), fmaf(sc.z, v.z, sh.z), fmaf(sc.w, v.w, sh.w));
+      if (e.act_relu) { a.x = fmaxf(a.x, 0.f); a.y = fmaxf(a.y, 0.f); a.z = fmaxf(a.z, 0.f); a.w = fmaxf(a.w, 0.f); }
+      *reinterpret_cast<float4*>(static_cast<float*>(e.out_act) + off) = a;
+    }
+  }
+}
+
+// ---- max-pool -------------------------------------------------------------------------------
+template <typename T>
+__global__ void maxpool_kernel(const T* __restrict__ in, int B, int H, int W, int C, int Ho, int Wo, int k,
+                               int stride, int pad, Epilogue e) {
+  constexpr int V = Vec<T>::N;
+  const int cv = C / V;
+  int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  int64_t total = int64_t(B) * Ho * Wo * cv;
+  if (idx >= total) return;
+  int c = int(idx % cv) * V;
+  int64_t pix = idx / cv;
+  int wo = int(pix % Wo);
+  int ho = int((pix / Wo) % Ho);
+  int b = int(pix / (int64_t(Wo) * Ho));
+  float best[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) best[i] = -3.402823466e+38f;
+  for (int ky = 0; ky < k; ++ky) {
+    int ih = ho * stride - pad + ky;
+    if (ih < 0 || ih >= H) continue;
+    for (int kx = 0; kx < k; ++kx) {
+      int iw = wo * stride - pad + kx;
+      if (iw < 0 || iw >= W) continue;
+      float v[V];
+      Vec<T>::load(in + ((int64_t(b) * H + ih) * W + iw) * C + c, v);
+#pragma unroll
+      for (int i = 0; i < V; ++i) best[i] = fmaxf(best[i], v[i]);
+    }
+  }
+  int64_t off = pix * C + c;
+  if (e.out) Vec<T>::store(static_cast<T*>(e.out) + off, best);
+  if (e.out_act) {
+    float a[V];
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      a[i] = fmaf(__ldg(e.act_scale + c + i), best[i], __ldg(e.act_shift + c + i));
+      if (e.act_relu) a[i] = fmaxf(a[i], 0.f);
+    }
+    Vec<T>::store(static_cast<T*>(e.out_act) + off, a);
+  }
+}
+
+// ---- global average pool (+ affine + ReLU on the way in) ------------------------------------
+template <typename T>
+__global__ void gap_kernel(const T* __restrict__ in, int B, int HW, int C, int Ctrue, const float* __restrict__ scale,
+                           const float* __restrict__ shift, int relu, float* __restrict__ out) {
+  constexpr int V = Vec<T>::N;
+  const int cv = C / V;
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * cv) return;
+  int c = (idx % cv) * V, b = idx / cv;
+  float s[V], t[V], acc[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) { s[i] = __ldg(scale + c + i); t[i] = __ldg(shift + c + i); acc[i] = 0.f; }
+  const T* p = in + int64_t(b) * HW * C + c;
+  for (int i = 0; i < HW; ++i) {
+    float v[V];
+    Vec<T>::load(p + int64_t(i) * C, v);
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      float x = fmaf(s[j], v[j], t[j]);
+      acc[j] += relu ? fmaxf(x, 0.f) : x;
+    }
+  }
+  const float inv = 1.f / float(HW);
+#pragma unroll
+  for (int j = 0; j < V; ++j)
+    if (c + j < Ctrue) out[int64_t(b) * Ctrue + c + j] = acc[j] * inv;
+}
+
+// ---- element-wise fallbacks -----------------------------------------------------------------
+template <typename T>
+__global__ void affine_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t pixels, int C,
+                              const float* __restrict__ scale, const float* __restrict__ shift, int relu) {
+  constexpr int V = Vec<T>::N;
+  const int cv = C / V;
+  int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= pixels * cv) return;
+  int c = int(idx % cv) * V;
+  int64_t off = (idx / cv) * C + c;
+  float v[V];
+  Vec<T>::load(in + off, v);
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    v[i] = fmaf(__ldg(scale + c + i), v[i], __ldg(shift + c + i));
+    if (relu) v[i] = fmaxf(v[i], 0.f);
+  }
+  Vec<T>::store(out + off, v);
+}
+
+template <typename T>
+__global__ void add_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ out, int64_t nvec) {
+  constexpr int V = Vec<T>::N;
+  int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= nvec) return;
+  float x[V], y[V];
+  Vec<T>::load(a + idx * V, x);
+  Vec<T>::load(b + idx * V, y);
+#pragma unroll
+  for (int i = 0; i < V; ++i) x[i] += y[i];
+  Vec<T>::store(out + idx * V, x);
+}
+
+// ---- softmax over rows (one CTA per row) ----------------------------------------------------
+__global__ void softmax_rows_kernel(const float* __restrict__ in, float* __restrict__ out, int N) {
+  __shared__ float red[32];
+  const float* x = in + int64_t(blockIdx.x) * N;
+  float* y = out + int64_t(blockIdx.x) * N;
+  float mx = -3.402823466e+38f;
+  for (int i = threadIdx.x; i < N; i += blockDim.x) mx = fmaxf(mx, x[i]);
+  for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  mx = red[0];
+  for (int i = 1; i < int(blockDim.x >> 5); ++i) mx = fmaxf(mx, red[i]);
+  __syncthreads();
+  float sum = 0.f;
+  for (int i = threadIdx.x; i < N; i += blockDim.x) sum += expf(x[i] - mx);
+  for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sum;
+  __syncthreads();
+  sum = 0.f;
+  for (int i = 0; i < int(blockDim.x >> 5); ++i) sum += red[i];
+  const float inv = 1.f / sum;
+  for (int i = threadIdx.x; i < N; i += blockDim.x) y[i] = expf(x[i] - mx) * inv;
+}
+
+}  // namespace
+
+// ---- launchers --------------------------------------------------------------------------------
+
+cudaError_t launch_input_xform(const float* nchw, void* out, DType dt, int B, int C, int H, int W, int Cpad,
+                               int Hp, int Wp, int off_h, int off_w, const float* scale, const float* shift,
+                               int relu, cudaStream_t s) {
+  int64_t total = int64_t(B) * H * W;
+  int block = 256, grid = grid_for(total, block);
+  switch (dt) {
+    case DType::F32:
+      input_xform_kernel<float><<<grid, block, 0, s>>>(nchw, static_cast<float*>(out), B, C, H, W, Cpad, Hp, Wp, off_h, off_w, scale, shift, relu);
+      break;
+    case DType::BF16:
+      input_xform_kernel<__nv_bfloat16><<<grid, block, 0, s>>>(nchw, static_cast<__nv_bfloat16*>(out), B, C, H, W, Cpad, Hp, Wp, off_h, off_w, scale, shift, relu);
+      break;
+    case DType::F16:
+      input_xform_kernel<__half><<<grid, block, 0, s>>>(nchw, static_cast<__half*>(out), B, C, H, W, Cpad, Hp, Wp, off_h, off_w, scale, shift, relu);
+      break;
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_conv_simt_f32(const float* in, const float* w, const ConvGeom& g, const Epilogue& e, cudaStream_t s) {
+  if (g.Cin % 4 || g.Cout % 4) return cudaErrorInvalidValue;
+  SimtConvParams p;
+  p.in = in; p.w = w; p.e = e; p.g = g;
+  p.M = g.B * g.Ho * g.Wo;
+  p.K = g.kh * g.kw * g.Cin;
+  dim3 grid((p.M + BM - 1) / BM, (g.Cout + BN - 1) / BN);
+  conv_simt_f32_kernel<<<grid, SIMT_THREADS, 0, s>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_maxpool(const void* in, DType dt, int B, int H, int W, int C, int Ho, int Wo, int k, int stride,
+                           int pad, const Epilogue& e, cudaStream_t s) {
+  int V = dt == DType::F32 ? 4 : 8;
+  if (C % V) return cudaErrorInvalidValue;
+  int64_t total = int64_t(B) * Ho * Wo * (C / V);
+  int block = 256, grid = grid_for(total, block);
+  switch (dt) {
+    case DType::F32: maxpool_kernel<float><<<grid, block, 0, s>>>(static_cast<const float*>(in), B, H, W, C, Ho, Wo, k, stride, pad, e); break;
+    case DType::BF16: maxpool_kernel<__nv_bfloat16><<<grid, block, 0, s>>>(static_cast<const __nv_bfloat16*>(in), B, H, W, C, Ho, Wo, k, stride, pad, e); break;
+    case DType::F16: maxpool_kernel<__half><<<grid, block, 0, s>>>(static_cast<const __half*>(in), B, H, W, C, Ho, Wo, k, stride, pad, e); break;
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_gap(const void* in, DType dt, int B, int HW, int C, int Ctrue, const float* scale,
+                       const float* shift, int relu, float* out, cudaStream_t s) {
+  int V = dt == DType::F32 ? 4 : 8;
+  if (C % V) return cudaErrorInvalidValue;
+  int total = B * (C / V);
+  int block = 128, grid = grid_for(total, block);
+  switch (dt) {
+    case DType::F32: gap_kernel<float><<<grid, block, 0, s>>>(static_cast<const float*>(in), B, HW, C, Ctrue, scale, shift, relu, out); break;
+    case DType::BF16: gap_kernel<__nv_bfloat16><<<grid, block, 0, s>>>(static_cast<const __nv_bfloat16*>(in), B, HW, C, Ctrue, scale, shift, relu, out); break;
+    case DType::F16: gap_kernel<__half><<<grid, block, 0, s>>>(static_cast<const __half*>(in), B, HW, C, Ctrue, scale, shift, relu, out); break;
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_affine(const void* in, void* out, DType dt, int64_t pixels, int C, const float* scale,
+                          const float* shift, int relu, cudaStream_t s) {
+  int V = dt == DType::F32 ? 4 : 8;
+  if (C % V) return cudaErrorInvalidValue;
+  int block = 256, grid = grid_for(pixels * (C / V), block);
+  switch (dt) {
+    case DType::F32: affine_kernel<float><<<grid, block, 0, s>>>(static_cast<const float*>(in), static_cast<float*>(out), pixels, C, scale, shift, relu); break;
+    case DType::BF16: affine_kernel<__nv_bfloat16><<<grid, block, 0, s>>>(static_cast<const __nv_bfloat16*>(in), static_cast<__nv_bfloat16*>(out), pixels, C, scale, shift, relu); break;
+    case DType::F16: affine_kernel<__half><<<grid, block, 0, s>>>(static_cast<const __half*>(in), static_cast<__half*>(out), pixels, C, scale, shift, relu); break;
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_add(const void* a, const void* b, void* out, DType dt, int64_t elems, cudaStream_t s) {
+  int V = dt == DType::F32 ? 4 : 8;
+  if (elems % V) return cudaErrorInvalidValue;
+  int block = 256, grid = grid_for(elems / V, block);
+  switch (dt) {
+    case DType::F32: add_kernel<float><<<grid, block, 0, s>>>(static_cast<const float*>(a), static_cast<const float*>(b), static_cast<float*>(out), elems / V); break;
+    case DType::BF16: add_kernel<__nv_bfloat16><<<grid, block, 0, s>>>(static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b), static_cast<__nv_bfloat16*>(out), elems / V); break;
+    case DType::F16: add_kernel<__half><<<grid, block, 0, s>>>(static_cast<const __half*>(a), static_cast<const __half*>(b), static_cast<__half*>(out), elems / V); break;
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_softmax_rows(const float* in, float* out, int B, int N, cudaStream_t s) {
+  softmax_rows_kernel<<<B, 256, 0, s>>>(in, out, N);
+  return cudaGetLastError();
+}
+
+}  // namespace rn

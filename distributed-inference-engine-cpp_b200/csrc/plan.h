@@ -1,0 +1,76 @@
+// Graph -> fused layer plan for the B200 ResNet backend.
+//
+// This is the host-side "graph optimiser" the reference gets from ONNX Runtime
+// (src/inference_engine.cpp:20 `SetGraphOptimizationLevel(ORT_ENABLE_EXTENDED)`), rebuilt for one
+// job: turn the parsed ONNX node list into the smallest sequence of device launches.
+// Fusions are decided from the graph (consumer counts), never from layer names:
+//   Conv -> BN            (BN the only consumer)      : folded into weights + bias
+//   ... -> ReLU           (only consumer)             : epilogue ReLU
+//   ... -> Add(x, other)  (only consumer)             : epilogue residual add
+//   T -> BN -> ReLU       (T made by Conv/MaxPool)    : second epilogue output relu(s*T+t); the raw
+//                                                       T is not written at all if nothing else reads it
+//   input -> BN           (BN the only consumer)      : applied while re-laying NCHW fp32 -> NHWC
+//   BN -> ReLU -> GlobalAveragePool                    : affine+ReLU applied inside the pooling kernel
+// Anything else falls back to a stand-alone element-wise layer; an operator outside the
+// supported set is an error (no CPU fallback).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "onnx_reader.h"
+
+namespace rn {
+
+enum class LayerKind : int { InputXform = 0, Conv, MaxPool, Affine, Add, Gap, Gemm, Softmax };
+const char* layer_kind_name(LayerKind k);
+
+struct PlanTensor {
+  int id = -1;
+  std::string name;        // ONNX value name it holds
+  int C = 0, H = 0, W = 0; // logical per-sample dims
+  int Cpad = 0;            // channels as stored in NHWC (>= C, zero-filled)
+  bool vec_f32 = false;    // [B, C] fp32 row (pool / Gemm / Softmax outputs) instead of NHWC activations
+  int def_layer = -1, last_use = -1;
+  bool is_output = false;
+  int64_t elems_per_sample() const { return vec_f32 ? int64_t(C) : int64_t(Cpad) * H * W; }
+};
+
+struct PlanLayer {
+  LayerKind kind = LayerKind::Conv;
+  std::string name;        // ONNX node names fused into this launch, '+'-joined
+  int in = -1;             // main input tensor
+  int in2 = -1;            // residual operand (Conv) / second operand (Add)
+  int out = -1;            // primary output (-1 when only the activated copy is kept)
+  int out_act = -1;        // relu?(act_scale * primary + act_shift)
+  // Conv / Gemm
+  int Cin = 0, Cout = 0, kh = 1, kw = 1, stride = 1, pad = 0;
+  std::vector<float> weight;   // Conv: [Cout][kh][kw][Cin_pad] (BN folded); Gemm: [N][K] (alpha folded)
+  std::vector<float> bias;     // [Cout] (always present; zeros if the graph has none)
+  bool relu = false;           // ReLU on (acc + bias), before the residual add
+  // second output / stand-alone affine / pooling prologue
+  std::vector<float> act_scale, act_shift;
+  bool act_relu = false;
+  // MaxPool
+  int pool_k = 0, pool_stride = 0, pool_pad = 0;
+  double macs_per_sample = 0;  // algorithmic multiply-accumulates (Conv/Gemm), for rooflines
+};
+
+struct Plan {
+  std::vector<PlanTensor> tensors;
+  std::vector<PlanLayer> layers;
+  std::string input_name, output_name;
+  std::vector<int64_t> input_shape, output_shape;   // as the reference reports them (-1 -> 1)
+  int64_t in_elems_per_sample = 0;                  // product of input dims after dim 0
+  int64_t out_elems_per_sample = 0;                 // product of output dims after dim 0
+  int in_C = 0, in_H = 0, in_W = 0;
+  int output_tensor = -1;
+  double total_macs_per_sample = 0;
+  std::string describe() const;                     // one line per layer (tests / DESIGN.md tables)
+};
+
+// channel_align: activations are stored with channels rounded up to this (4 for the fp32 path,
+// 8 for 16-bit paths; the 3-channel network input is always stored as 4).
+Plan build_plan(const OnnxModel& model, int channel_align);
+
+}  // namespace rn
