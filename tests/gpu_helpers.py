@@ -1,0 +1,121 @@
+"""Shared helpers for the GPU parity tests: torch provides device memory; the CPU oracle (torch-CPU
+float64 conv on the same rounded operands) provides the expected values."""
+import ctypes as C
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+import b200rn_loader
+
+pkg = b200rn_loader.load_package()
+lib = pkg.lib
+
+TORCH_DT = {0: torch.float32, 1: torch.bfloat16, 2: torch.float16}
+# relative / absolute tolerance on conv outputs of O(1): storage rounding of the output dominates
+TOL = {0: (2e-5, 2e-5), 1: (1.2e-2, 1.2e-2), 2: (1.5e-3, 1.5e-3)}
+
+
+def conv_case(dtype, B, H, W, Cin, Cout, k, stride, pad, relu=0, residual=False, want_out=True, want_act=False,
+              act_relu=1, seed=0):
+    """Runs b200rn_conv2d on random data; returns dict(err_out, err_act, ...) vs a float64 CPU conv."""
+    g = torch.Generator().manual_seed(seed)
+    tdt = TORCH_DT[dtype]
+    x = torch.randn(B, Cin, H, W, generator=g).to(tdt)
+    w = (torch.randn(Cout, Cin, k, k, generator=g) * (2.0 / (Cin * k * k)) ** 0.5).to(tdt)
+    bias = torch.randn(Cout, generator=g) * 0.5
+    Ho, Wo = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+    res = torch.randn(B, Cout, Ho, Wo, generator=g).to(tdt) if residual else None
+    s2 = torch.rand(Cout, generator=g) + 0.5
+    t2 = torch.randn(Cout, generator=g) * 0.3
+    # expected (float64 on the rounded operands)
+    y = F.conv2d(x.double(), w.double(), bias.double(), stride=stride, padding=pad)
+    if relu:
+        y = y.clamp_min(0)
+    if residual:
+        y = y + res.double()
+    ya = y * s2.double().view(1, -1, 1, 1) + t2.double().view(1, -1, 1, 1)
+    if act_relu:
+        ya = ya.clamp_min(0)
+    # device operands, NHWC
+    d_x = x.permute(0, 2, 3, 1).contiguous().cuda()
+    d_res = res.permute(0, 2, 3, 1).contiguous().cuda() if residual else None
+    d_out = torch.full((B, Ho, Wo, Cout), float("nan"), dtype=tdt, device="cuda") if want_out else None
+    d_act = torch.full((B, Ho, Wo, Cout), float("nan"), dtype=tdt, device="cuda") if want_act else None
+    w_khwc = np.ascontiguousarray(w.float().permute(0, 2, 3, 1).numpy())   # [Cout][kh][kw][Cin]
+    b_np = bias.numpy().astype(np.float32)
+    s_np, t_np = s2.numpy().astype(np.float32), t2.numpy().astype(np.float32)
+    torch.cuda.synchronize()
+    rc = lib.b200rn_conv2d(dtype, d_x.data_ptr(), B, H, W, Cin, pkg.fptr(w_khwc), pkg.fptr(b_np), Cout, k, k, stride,
+                           pad, relu, d_res.data_ptr() if residual else None,
+                           d_out.data_ptr() if want_out else None, d_act.data_ptr() if want_act else None,
+                           pkg.fptr(s_np), pkg.fptr(t_np), act_relu)
+    out = {"rc": rc, "msg": lib.b200rn_global_error().decode() if rc else ""}
+    if rc:
+        return out
+    rtol, atol = TOL[dtype]
+
+    def cmp(dev, ref):
+        got = dev.float().cpu().permute(0, 3, 1, 2).double()
+        bad = ~torch.isfinite(got)
+        err = (got - ref).abs()
+        lim = atol + rtol * ref.abs()
+        return {"max_err": float(err[~bad].max()) if (~bad).any() else float("nan"), "nonfinite": int(bad.sum()),
+                "viol": int((err > lim).sum() + bad.sum()), "n": got.numel(),
+                "worst_ratio": float((err / lim)[~bad].max()) if (~bad).any() else float("inf")}
+    if want_out:
+        out["out"] = cmp(d_out, y)
+    if want_act:
+        out["act"] = cmp(d_act, ya)
+    return out
+
+
+def stem_case(dtype, B, H, W, Cout=64, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    tdt = TORCH_DT[dtype]
+    x = torch.randn(B, 3, H, W, generator=g)
+    s = torch.rand(3, generator=g) + 0.5
+    t = torch.randn(3, generator=g) * 0.2
+    w = (torch.randn(Cout, 3, 7, 7, generator=g) * (2.0 / 147) ** 0.5).to(tdt)
+    bias = torch.randn(Cout, generator=g) * 0.5
+    xa = (x * s.view(1, 3, 1, 1) + t.view(1, 3, 1, 1)).to(tdt)      # what the re-layout kernel stores
+    y = F.conv2d(xa.double(), w.double(), bias.double(), stride=2, padding=3).clamp_min(0)
+    Ho, Wo = y.shape[2], y.shape[3]
+    d_x = x.contiguous().cuda()
+    d_out = torch.full((B, Ho, Wo, Cout), float("nan"), dtype=tdt, device="cuda")
+    w4 = np.zeros((Cout, 7, 7, 4), dtype=np.float32)
+    w4[..., :3] = w.float().permute(0, 2, 3, 1).numpy()
+    b_np = bias.numpy().astype(np.float32)
+    s_np, t_np = s.numpy().astype(np.float32), t.numpy().astype(np.float32)
+    torch.cuda.synchronize()
+    rc = lib.b200rn_stem_conv(dtype, d_x.data_ptr(), B, H, W, pkg.fptr(s_np), pkg.fptr(t_np), pkg.fptr(w4),
+                              pkg.fptr(b_np), Cout, 1, d_out.data_ptr())
+    out = {"rc": rc, "msg": lib.b200rn_global_error().decode() if rc else ""}
+    if rc:
+        return out
+    rtol, atol = TOL[dtype]
+    got = d_out.float().cpu().permute(0, 3, 1, 2).double()
+    bad = ~torch.isfinite(got)
+    err = (got - y).abs()
+    lim = 2 * atol + 2 * rtol * y.abs()     # the fused input affine is rounded once more than the reference
+    out["out"] = {"max_err": float(err[~bad].max()) if (~bad).any() else float("nan"), "nonfinite": int(bad.sum()),
+                  "viol": int((err > lim).sum() + bad.sum()), "n": got.numel(),
+                  "worst_ratio": float((err / lim)[~bad].max()) if (~bad).any() else float("inf")}
+    return out
+
+
+CONV_CASES = [
+    # name, kwargs
+    ("1x1 s1 64->64 @56 B2", dict(B=2, H=56, W=56, Cin=64, Cout=64, k=1, stride=1, pad=0)),
+    ("1x1 s1 256->128 @14 B3", dict(B=3, H=14, W=14, Cin=256, Cout=128, k=1, stride=1, pad=0, relu=1)),
+    ("3x3 s1 64->64 @56 B2", dict(B=2, H=56, W=56, Cin=64, Cout=64, k=3, stride=1, pad=1, relu=1)),
+    ("3x3 s1 128->128 @28 B5", dict(B=5, H=28, W=28, Cin=128, Cout=128, k=3, stride=1, pad=1, relu=1)),
+    ("1x1 s2 256->512 @56 B2", dict(B=2, H=56, W=56, Cin=256, Cout=512, k=1, stride=2, pad=0)),
+    ("3x3 s2 128->128 @56 B2", dict(B=2, H=56, W=56, Cin=128, Cout=128, k=3, stride=2, pad=1, relu=1)),
+    ("3x3 s1 512->512 @7 B4", dict(B=4, H=7, W=7, Cin=512, Cout=512, k=3, stride=1, pad=1, relu=1)),
+    ("1x1 64->256 @14 res+dual", dict(B=3, H=14, W=14, Cin=64, Cout=256, k=1, stride=1, pad=0, residual=True,
+                                      want_out=True, want_act=True)),
+    ("1x1 512->2048 @7 res act-only", dict(B=2, H=7, W=7, Cin=512, Cout=2048, k=1, stride=1, pad=0, residual=True,
+                                           want_out=False, want_act=True)),
+    ("3x3 s2 512->512 @14 B33", dict(B=33, H=14, W=14, Cin=512, Cout=512, k=3, stride=2, pad=1, relu=1)),
+]

@@ -1,0 +1,171 @@
+"""GPU parity of the whole hot path through the engine's public surface (the Python mirror of
+InferenceEngine over the C ABI) against the CPU oracle (oracle/resnet_oracle.py, fp32, unfused).
+
+Bars (BASELINE.json north_star):
+  exact mode (fp32 storage + fp32 accumulate): max-abs logit error <= 1e-3
+  bf16 / fp16 tensor-core modes: 100% top-1 agreement on every input whose oracle top-1/top-2 margin
+  exceeds 4x that mode's measured max-abs error (closer calls are counted and reported, not asserted --
+  with random weights a near-tie is a coin flip for ANY finite-precision implementation), and a bounded
+  max-abs error (bf16 <= 0.25, fp16 <= 0.03 on logits with std ~5)."""
+import os
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+import b200rn_loader  # noqa: E402
+from oracle import resnet_oracle  # noqa: E402
+from tools import make_resnet50v2_onnx as gen  # noqa: E402
+
+pkg = b200rn_loader.load_package()
+ABS_BOUND = {"exact": 1e-3, "bf16": 0.25, "fp16": 0.03}
+
+
+def parity_inputs(n, shape, seed=0):
+    """N(0,1) images plus structured ones so that the top-1 class varies: smooth gradients,
+    scaled noise, constant planes, all-zeros, and the 3-float benchmark payload zero-padded."""
+    rs = np.random.RandomState(seed)
+    c, h, w = shape
+    xs = []
+    yy, xx = np.meshgrid(np.linspace(-1, 1, h), np.linspace(-1, 1, w), indexing="ij")
+    for i in range(n):
+        kind = i % 4
+        if kind == 0:
+            x = rs.randn(c, h, w)
+        elif kind == 1:
+            a = rs.randn(c, 3)
+            x = a[:, 0, None, None] * yy + a[:, 1, None, None] * xx + a[:, 2, None, None] + 0.3 * rs.randn(c, h, w)
+        elif kind == 2:
+            x = rs.randn(c, h, w) * rs.uniform(0.2, 3.0)
+        else:
+            f = rs.uniform(1, 6, size=2)
+            x = np.sin(f[0] * np.pi * yy + rs.uniform(0, 6))[None] * np.cos(f[1] * np.pi * xx)[None] * rs.randn(c, 1, 1) * 2
+        xs.append(x.astype(np.float32))
+    return np.stack(xs)
+
+
+@pytest.fixture(scope="module")
+def r50(tmp_path_factory):
+    p = str(tmp_path_factory.mktemp("m") / "r50.onnx")
+    gen.write_model(p, "resnet50", seed=0)
+    return p
+
+
+@pytest.fixture(scope="module")
+def r50_oracle(r50):
+    x = parity_inputs(32, (3, 224, 224), seed=0)
+    eng = resnet_oracle.OracleEngine(r50)
+    ref = np.stack(eng.batch_predict(list(x.reshape(len(x), -1))))
+    return x, ref
+
+
+@pytest.mark.parametrize("mode", ["exact", "fp16", "bf16"])
+def test_resnet50_logits_vs_oracle(r50, r50_oracle, mode):
+    x, ref = r50_oracle
+    eng = pkg.Engine(r50, mode=mode, max_batch=32)
+    assert eng.get_input_shape() == [1, 3, 224, 224] and eng.get_output_shape() == [1, 1000]
+    out = np.stack(eng.batch_predict(list(x.reshape(len(x), -1))))
+    eng.close()
+    assert np.isfinite(out).all()
+    err = np.abs(out - ref).max()
+    top = np.sort(ref, axis=1)
+    margin = top[:, -1] - top[:, -2]
+    agree = out.argmax(1) == ref.argmax(1)
+    decided = margin > 4 * max(err, 1e-6)
+    print("\n[%s] max-abs %.3e; top-1 agreement %d/%d (decided inputs: %d, all agree: %s); distinct top-1 classes %d"
+          % (mode, err, agree.sum(), len(agree), decided.sum(), bool(agree[decided].all()), len(set(ref.argmax(1)))))
+    assert err <= ABS_BOUND[mode], "max-abs %.3e exceeds the %s bound %.1e" % (err, mode, ABS_BOUND[mode])
+    assert agree[decided].all()
+    if mode == "exact":
+        assert agree.all()
+
+
+def test_golden_logits(r50, golden_dir):
+    """Committed oracle outputs (tests/golden/make_logits_golden.py) on the deterministic fixture."""
+    path = os.path.join(golden_dir, "resnet50_logits_seed0.npz")
+    if not os.path.exists(path):
+        pytest.skip("golden logits not generated")
+    g = np.load(path)
+    x = parity_inputs(int(g["n"]), (3, 224, 224), seed=int(g["seed"]))
+    eng = pkg.Engine(r50, mode="exact", max_batch=8)
+    out = eng.infer_packed(x)
+    eng.close()
+    assert np.abs(out - g["logits_fp32"]).max() <= 1e-3
+    assert np.abs(out - g["logits_fp64"]).max() <= 1e-3
+
+
+@pytest.mark.parametrize("mode", ["exact", "fp16"])
+def test_batch_semantics(tmp_path, mode):
+    """Reference semantics of batchPredict / predict (src/inference_engine.cpp:89-209) on a small model."""
+    p = str(tmp_path / "s.onnx")
+    gen.write_model(p, "small64", seed=3)
+    eng = pkg.Engine(p, mode=mode, max_batch=4)       # max_batch < batch: exercises slicing + both slots
+    ora = resnet_oracle.OracleEngine(p)
+    per = 3 * 64 * 64
+    rs = np.random.RandomState(1)
+    full = rs.randn(per).astype(np.float32)
+    inputs = [full, full[:100], np.asarray([1.0, 2.0, 3.0], np.float32), np.zeros(0, np.float32),
+              rs.randn(per).astype(np.float32), rs.randn(per).astype(np.float32), full[:per - 1],
+              rs.randn(per).astype(np.float32), rs.randn(7).astype(np.float32)]
+    got = np.stack(eng.batch_predict(inputs))
+    ref = np.stack(ora.batch_predict(inputs))
+    tol = 1e-3 if mode == "exact" else 0.05
+    assert got.shape == (9, 100) and np.abs(got - ref).max() <= tol
+    assert eng.batch_predict([]) == []                                   # :137-139
+    # batch composition must not change a sample's result
+    alone = eng.batch_predict([inputs[4]])[0]
+    assert np.abs(alone - got[4]).max() <= (1e-5 if mode == "exact" else 2e-2)
+    # predict pads and truncates (:100-103)
+    longer = np.concatenate([full, rs.randn(50).astype(np.float32)])
+    assert np.abs(eng.predict(longer) - ora.predict(longer)).max() <= tol
+    assert np.abs(eng.predict(full[:10]) - ora.predict(full[:10])).max() <= tol
+    # documented divergence: an over-long sample in batchPredict is rejected
+    with pytest.raises(pkg.B200RNError, match="holds"):
+        eng.batch_predict([longer])
+    # packed and device-resident forms agree with the ragged one
+    x = np.stack([inputs[0], inputs[4], inputs[5]]).reshape(3, 3, 64, 64)
+    packed = eng.infer_packed(x)
+    assert np.abs(packed - got[[0, 4, 5]]).max() <= (1e-5 if mode == "exact" else 2e-2)
+    d_in = torch.from_numpy(x).cuda()
+    d_out = torch.empty(3, 100, dtype=torch.float32, device="cuda")
+    eng.infer_device_ptr(d_in.data_ptr(), 3, d_out.data_ptr())
+    assert np.abs(d_out.cpu().numpy() - packed).max() <= 1e-6
+    eng.close()
+
+
+def test_double_buffered_submit(tmp_path):
+    p = str(tmp_path / "s.onnx")
+    gen.write_model(p, "small64", seed=4)
+    eng = pkg.Engine(p, mode="fp16", max_batch=8)
+    rs = np.random.RandomState(2)
+    xs = [rs.randn(8, 3, 64, 64).astype(np.float32) for _ in range(4)]
+    want = [eng.infer_packed(x) for x in xs]
+    outs = [np.empty((8, 100), np.float32) for _ in xs]
+    eng.submit_ptr(0, xs[0].ctypes.data, 8, outs[0].ctypes.data)
+    eng.submit_ptr(1, xs[1].ctypes.data, 8, outs[1].ctypes.data)
+    eng.wait(0)
+    eng.submit_ptr(0, xs[2].ctypes.data, 8, outs[2].ctypes.data)
+    eng.wait(1)
+    eng.submit_ptr(1, xs[3].ctypes.data, 8, outs[3].ctypes.data)
+    eng.wait(0)
+    eng.wait(1)
+    for o, w in zip(outs, want):
+        assert np.array_equal(o, w)
+    with pytest.raises(pkg.B200RNError):
+        eng.wait(0)                       # nothing submitted
+    eng.close()
+
+
+def test_softmax_graph_and_generic_fallback_layers(tmp_path):
+    """A graph ending in Softmax (not in the v2-7 file) runs, and changes results exactly as the op says."""
+    p = str(tmp_path / "sm.onnx")
+    gen.write_model(p, "small64", seed=5, softmax=True)
+    eng = pkg.Engine(p, mode="exact", max_batch=4)
+    ora = resnet_oracle.OracleEngine(p)
+    x = resnet_oracle.synthetic_inputs(3, 5, (3, 64, 64))
+    got = eng.infer_packed(x)
+    ref = np.stack(ora.batch_predict(list(x.reshape(3, -1))))
+    assert np.abs(got - ref).max() <= 1e-5 and np.allclose(got.sum(1), 1.0, atol=1e-5)
+    eng.close()

@@ -120,7 +120,7 @@ class Builder:
         self.rs = np.random.RandomState(seed)
         self.nodes = []
         self.inits = []  # (name, array)
-        self.n = 0
+        self.ops = []    # (kind, inputs, output, params) for the calibration forward
 
     def init(self, name, arr):
         self.inits.append((name, np.asarray(arr, dtype=np.float32)))
@@ -137,6 +137,7 @@ class Builder:
         out = name + "_fwd"
         self.nodes.append(node("BatchNormalization", ins, [out], name + "_fwd",
                                [attr_f("epsilon", eps), attr_f("momentum", 0.9), attr_i("spatial", 1)]))
+        self.ops.append(("bn", [x], out, dict(g=gamma, b=beta, m=mean, v=var, eps=eps)))
         return out
 
     def conv(self, x, cin, cout, k, stride, pad, name):
@@ -149,21 +150,75 @@ class Builder:
                                 attr_ints("kernel_shape", [k, k]),
                                 attr_ints("pads", [pad, pad, pad, pad]),
                                 attr_ints("strides", [stride, stride])]))
+        self.ops.append(("conv", [x], out, dict(w=w, stride=stride, pad=pad)))
         return out
 
     def relu(self, x, name):
         out = name + "_fwd"
         self.nodes.append(node("Relu", [x], [out], name + "_fwd"))
+        self.ops.append(("relu", [x], out, {}))
         return out
 
     def simple(self, op, ins, name, attrs=()):
         out = name + "_fwd"
         self.nodes.append(node(op, ins, [out], name + "_fwd", attrs))
+        self.ops.append((op.lower(), list(ins), out, {}))
         return out
+
+    def pooled_features(self, x):
+        """Calibration forward (torch CPU, fp32) of everything recorded so far; returns the last value."""
+        import torch
+        import torch.nn.functional as F
+        env = {"data": torch.from_numpy(x)}
+        f32 = lambda a: torch.from_numpy(np.asarray(a, dtype=np.float32))
+        last = None
+        with torch.no_grad():
+            for kind, ins, out, p in self.ops:
+                a = env[ins[0]]
+                if kind == "bn":
+                    sh = (1, -1, 1, 1)
+                    y = (a - f32(p["m"]).view(sh)) / torch.sqrt(f32(p["v"]).view(sh) + p["eps"]) * f32(p["g"]).view(sh) + f32(p["b"]).view(sh)
+                elif kind == "conv":
+                    y = F.conv2d(a, f32(p["w"]), None, stride=p["stride"], padding=p["pad"])
+                elif kind == "relu":
+                    y = torch.relu(a)
+                elif kind == "maxpool":
+                    y = F.max_pool2d(a, 3, stride=2, padding=1)
+                elif kind == "add":
+                    y = a + env[ins[1]]
+                elif kind == "globalaveragepool":
+                    y = a.mean(dim=(2, 3), keepdim=True)
+                else:
+                    raise ValueError(kind)
+                env[out] = y
+                last = y
+        return last.reshape(last.shape[0], -1).numpy()
+
+
+def calibration_inputs(n, shape, seed=777):
+    """Mixed noise / smooth / scaled images used only to centre the synthetic classifier."""
+    rs = np.random.RandomState(seed)
+    c, h, w = shape
+    yy, xx = np.meshgrid(np.linspace(-1, 1, h), np.linspace(-1, 1, w), indexing="ij")
+    xs = []
+    for i in range(n):
+        k = i % 4
+        if k == 0:
+            x = rs.randn(c, h, w)
+        elif k == 1:
+            a = rs.randn(c, 3)
+            x = a[:, 0, None, None] * yy + a[:, 1, None, None] * xx + a[:, 2, None, None] + 0.3 * rs.randn(c, h, w)
+        elif k == 2:
+            x = rs.randn(c, h, w) * rs.uniform(0.2, 3.0)
+        else:
+            f = rs.uniform(1, 6, size=2)
+            x = np.sin(f[0] * np.pi * yy + rs.uniform(0, 6))[None] * np.cos(f[1] * np.pi * xx)[None] * rs.randn(c, 1, 1) * 2
+        xs.append(x.astype(np.float32))
+    return np.stack(xs)
 
 
 def build(seed=0, image=224, stem=64, widths=(256, 512, 1024, 2048), blocks=(3, 4, 6, 3),
-          classes=1000, batch_dim="N", float_data_for_small=True, softmax=False):
+          classes=1000, batch_dim="N", float_data_for_small=True, softmax=False, calib=None, calibrate_out=None):
     b = Builder(seed)
     p = "resnetv24_"
     x = b.bn("data", 3, p + "batchnorm0", var_est=1.0, fix_gamma=True)
@@ -208,9 +263,20 @@ def build(seed=0, image=224, stem=64, widths=(256, 512, 1024, 2048), blocks=(3, 
     x = b.bn(x, cin, p + "batchnorm2", var_est=trunk_var)
     x = b.relu(x, p + "relu1")
     x = b.simple("GlobalAveragePool", [x], p + "pool1")
+    if calibrate_out is not None:
+        feats = b.pooled_features(calibration_inputs(48, (3, image, image)))
+        np.savez_compressed(calibrate_out, mean=feats.mean(0).astype(np.float32), std=feats.std(0).astype(np.float32))
+        calib = dict(mean=feats.mean(0), std=feats.std(0))
+    b.ops = []
     x = b.simple("Flatten", [x], p + "flatten0", [attr_i("axis", 1)])
     wfc = b.rs.randn(classes, cin) * np.sqrt(1.0 / cin) * 4.0
     bfc = 0.5 * b.rs.randn(classes)
+    if calib is not None:
+        # Make the classifier read standardised deviations from the mean pooled feature, so that the
+        # winning class depends on the input (a random deep net's pooled features barely move, and an
+        # uncalibrated FC would crown the same class for every image).
+        wfc = wfc / np.maximum(np.asarray(calib["std"], dtype=np.float64), 1e-3)[None, :]
+        bfc = bfc - wfc @ np.asarray(calib["mean"], dtype=np.float64)
     out = p + "dense0_fwd"
     b.nodes.append(node("Gemm", [x, b.init(p + "dense0_weight", wfc), b.init(p + "dense0_bias", bfc)],
                         [out], p + "dense0_fwd",
@@ -248,9 +314,24 @@ PRESETS = {
 }
 
 
-def write_model(path, preset="resnet50", seed=0, **kw):
+def calib_path(preset, seed):
+    import os
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "calib_%s_seed%d.npz" % (preset, seed))
+
+
+def write_model(path, preset="resnet50", seed=0, calibrate=False, **kw):
+    """Writes the model.  If tools/calib_<preset>_seed<seed>.npz exists (committed for resnet50/seed 0)
+    the classifier is centred with it, which keeps the weights bit-reproducible across machines;
+    calibrate=True recomputes that file here with a torch-CPU forward first."""
+    import os
     cfg = dict(PRESETS[preset])
     cfg.update(kw)
+    cp = calib_path(preset, seed)
+    if calibrate:
+        build(seed=seed, calibrate_out=cp, **cfg)
+    if os.path.exists(cp) and "calib" not in cfg:
+        z = np.load(cp)
+        cfg["calib"] = dict(mean=z["mean"], std=z["std"])
     data = build(seed=seed, **cfg)
     with open(path, "wb") as f:
         f.write(data)
@@ -264,13 +345,14 @@ def main(argv=None):
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--softmax", action="store_true", help="append a Softmax node (not in the v2-7 graph)")
     ap.add_argument("--static-batch", type=int, default=0, help="write a fixed batch dim instead of 'N'")
+    ap.add_argument("--calibrate", action="store_true", help="(re)compute tools/calib_<preset>_seed<seed>.npz first")
     a = ap.parse_args(argv)
     kw = {}
     if a.softmax:
         kw["softmax"] = True
     if a.static_batch:
         kw["batch_dim"] = a.static_batch
-    n = write_model(a.out, a.preset, a.seed, **kw)
+    n = write_model(a.out, a.preset, a.seed, calibrate=a.calibrate, **kw)
     print("wrote %s (%d bytes)" % (a.out, n))
 
 
