@@ -56,7 +56,7 @@ _sig("b200rn_layer_count", C.c_int, [_vp])
 _sig("b200rn_layer_name", C.c_int, [_vp, C.c_int, C.c_char_p, C.c_size_t])
 _sig("b200rn_profile_layers", C.c_int, [_vp, _vp, C.c_size_t, C.c_int, _fp, C.POINTER(C.c_int),
                                         C.POINTER(C.c_double), C.POINTER(C.c_double)])
-_sig("b200rn_time_forward", C.c_int, [_vp, _vp, C.c_size_t, C.c_int, _fp])
+_sig("b200rn_time_forward", C.c_int, [_vp, C.POINTER(_vp), C.c_int, C.c_size_t, C.c_int, _fp])
 _sig("b200rn_conv2d", C.c_int, [C.c_int, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _fp, _fp, C.c_int, C.c_int,
                                 C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _fp, _fp, C.c_int])
 _sig("b200rn_stem_conv", C.c_int, [C.c_int, _vp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp, C.c_int, C.c_int, _vp])
@@ -174,9 +174,11 @@ class Engine:
     def wait(self, slot):
         self._check(lib.b200rn_wait(self._h, slot), "b200rn_wait")
 
-    def time_forward(self, d_in, batch, iters):
+    def time_forward(self, d_inputs, batch, iters):
+        """d_inputs: list of device pointers (int) to [batch, C, H, W] fp32 batches, used round-robin."""
+        arr = (_vp * len(d_inputs))(*d_inputs)
         ms = C.c_float()
-        self._check(lib.b200rn_time_forward(self._h, d_in, batch, iters, C.byref(ms)), "b200rn_time_forward")
+        self._check(lib.b200rn_time_forward(self._h, arr, len(d_inputs), batch, iters, C.byref(ms)), "b200rn_time_forward")
         return ms.value
 
     def layer_count(self):

@@ -589,8 +589,8 @@ int b200rn_profile_layers(b200rn_t* h, const float* d_nchw, size_t batch, int it
   });
 }
 
-int b200rn_time_forward(b200rn_t* h, const float* d_nchw, size_t batch, int iters, float* ms_total) {
-  if (!h || !d_nchw || !ms_total || batch == 0 || iters <= 0) { g_error = "b200rn_time_forward: bad argument"; return B200RN_ERR_ARG; }
+int b200rn_time_forward(b200rn_t* h, const float* const* d_inputs, int n_inputs, size_t batch, int iters, float* ms_total) {
+  if (!h || !d_inputs || n_inputs <= 0 || !ms_total || batch == 0 || iters <= 0) { g_error = "b200rn_time_forward: bad argument"; return B200RN_ERR_ARG; }
   std::lock_guard<std::mutex> lk(h->mu);
   return guarded(h, [&] {
     CK(cudaSetDevice(h->device));
@@ -600,12 +600,13 @@ int b200rn_time_forward(b200rn_t* h, const float* d_nchw, size_t batch, int iter
     CK(cudaEventCreate(&b));
     CK(cudaStreamSynchronize(h->s_compute));
     CK(cudaEventRecord(a, h->s_compute));
-    for (int i = 0; i < iters; ++i) h->forward(int(batch), d_nchw, h->slot[0].d_out, h->s_compute);
+    for (int i = 0; i < iters; ++i) h->forward(int(batch), d_inputs[i % n_inputs], h->slot[0].d_out, h->s_compute);
     CK(cudaEventRecord(b, h->s_compute));
     CK(cudaEventSynchronize(b));
     CK(cudaEventElapsedTime(ms_total, a, b));
     cudaEventDestroy(a);
     cudaEventDestroy(b);
+    h->check_kernel_health();
   });
 }
 

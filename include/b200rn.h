@@ -114,8 +114,10 @@ int b200rn_profile_layers(b200rn_t* h, const float* d_nchw, size_t batch, int it
 int b200rn_layer_name(const b200rn_t* h, int i, char* buf, size_t cap);
 
 /* Times `iters` back-to-back forwards of `batch` on the device (CUDA events on the compute stream,
- * inputs resident in HBM); returns total milliseconds in *ms_total. */
-int b200rn_time_forward(b200rn_t* h, const float* d_nchw, size_t batch, int iters, float* ms_total);
+ * inputs resident in HBM, taken round-robin from the n_inputs device batches so that consecutive
+ * steps do not re-read a cached input); returns total milliseconds in *ms_total. */
+int b200rn_time_forward(b200rn_t* h, const float* const* d_inputs, int n_inputs, size_t batch, int iters,
+                        float* ms_total);
 
 /* ---- single-operator entry point (tests of the conv kernels against a framework reference) ----
  * NHWC convolution with the fused epilogue, device pointers, on the current device.

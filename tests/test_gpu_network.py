@@ -6,7 +6,15 @@ Bars (BASELINE.json north_star):
   bf16 / fp16 tensor-core modes: 100% top-1 agreement on every input whose oracle top-1/top-2 margin
   exceeds 4x that mode's measured max-abs error (closer calls are counted and reported, not asserted --
   with random weights a near-tie is a coin flip for ANY finite-precision implementation), and a bounded
-  max-abs error (bf16 <= 0.25, fp16 <= 0.03 on logits with std ~5)."""
+  max-abs error.
+
+Two fixtures of the same topology and conv/BN weights, differing only in the classifier:
+  "plain"      He-random FC: logits (std ~5) are dominated by the input-independent part, so every input
+               has the same top-1 class; well conditioned -> tight absolute bounds (fp16 0.03, bf16 0.25).
+  "calibrated" FC reads standardised deviations of the pooled features (tools/make_resnet50v2_onnx.py),
+               so the top-1 class depends on the input (27 distinct classes over the 32 parity inputs,
+               logit std ~3); this amplifies feature error ~10x -> looser absolute bounds (fp16 0.2,
+               bf16 1.5) and a meaningful top-1 statistic."""
 import os
 
 import numpy as np
@@ -20,7 +28,8 @@ from oracle import resnet_oracle  # noqa: E402
 from tools import make_resnet50v2_onnx as gen  # noqa: E402
 
 pkg = b200rn_loader.load_package()
-ABS_BOUND = {"exact": 1e-3, "bf16": 0.25, "fp16": 0.03}
+ABS_BOUND = {"plain": {"exact": 1e-3, "bf16": 0.25, "fp16": 0.03},
+             "calibrated": {"exact": 1e-3, "bf16": 1.5, "fp16": 0.2}}
 
 
 def parity_inputs(n, shape, seed=0):
@@ -54,29 +63,43 @@ def r50(tmp_path_factory):
 
 
 @pytest.fixture(scope="module")
-def r50_oracle(r50):
+def r50_plain(tmp_path_factory):
+    p = str(tmp_path_factory.mktemp("m") / "r50_plain.onnx")
+    gen.write_model(p, "resnet50", seed=0, calib=None)
+    return p
+
+
+@pytest.fixture(scope="module")
+def oracle_logits(r50, r50_plain):
     x = parity_inputs(32, (3, 224, 224), seed=0)
-    eng = resnet_oracle.OracleEngine(r50)
-    ref = np.stack(eng.batch_predict(list(x.reshape(len(x), -1))))
-    return x, ref
+    out = {}
+    for name, path in (("calibrated", r50), ("plain", r50_plain)):
+        eng = resnet_oracle.OracleEngine(path)
+        out[name] = (path, np.stack(eng.batch_predict(list(x.reshape(len(x), -1)))))
+    return x, out
 
 
+@pytest.mark.parametrize("fixture", ["plain", "calibrated"])
 @pytest.mark.parametrize("mode", ["exact", "fp16", "bf16"])
-def test_resnet50_logits_vs_oracle(r50, r50_oracle, mode):
-    x, ref = r50_oracle
-    eng = pkg.Engine(r50, mode=mode, max_batch=32)
+def test_resnet50_logits_vs_oracle(oracle_logits, mode, fixture):
+    x, per_fixture = oracle_logits
+    path, ref = per_fixture[fixture]
+    eng = pkg.Engine(path, mode=mode, max_batch=32)
     assert eng.get_input_shape() == [1, 3, 224, 224] and eng.get_output_shape() == [1, 1000]
     out = np.stack(eng.batch_predict(list(x.reshape(len(x), -1))))
     eng.close()
     assert np.isfinite(out).all()
     err = np.abs(out - ref).max()
+    rel = np.linalg.norm(out - ref) / np.linalg.norm(ref - ref.mean())
     top = np.sort(ref, axis=1)
     margin = top[:, -1] - top[:, -2]
     agree = out.argmax(1) == ref.argmax(1)
     decided = margin > 4 * max(err, 1e-6)
-    print("\n[%s] max-abs %.3e; top-1 agreement %d/%d (decided inputs: %d, all agree: %s); distinct top-1 classes %d"
-          % (mode, err, agree.sum(), len(agree), decided.sum(), bool(agree[decided].all()), len(set(ref.argmax(1)))))
-    assert err <= ABS_BOUND[mode], "max-abs %.3e exceeds the %s bound %.1e" % (err, mode, ABS_BOUND[mode])
+    print("\n[%s/%s] max-abs %.3e (logit std %.2f, rel-L2 %.2e); top-1 agreement %d/%d (decided inputs: %d, all agree: %s); "
+          "distinct top-1 classes %d" % (fixture, mode, err, ref.std(), rel, agree.sum(), len(agree), decided.sum(),
+                                         bool(agree[decided].all()), len(set(ref.argmax(1)))))
+    bound = ABS_BOUND[fixture][mode]
+    assert err <= bound, "max-abs %.3e exceeds the %s/%s bound %.1e" % (err, fixture, mode, bound)
     assert agree[decided].all()
     if mode == "exact":
         assert agree.all()
