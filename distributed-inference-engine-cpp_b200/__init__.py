@@ -60,6 +60,8 @@ _sig("b200rn_time_forward", C.c_int, [_vp, C.POINTER(_vp), C.c_int, C.c_size_t, 
 _sig("b200rn_conv2d", C.c_int, [C.c_int, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _fp, _fp, C.c_int, C.c_int,
                                 C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _fp, _fp, C.c_int])
 _sig("b200rn_stem_conv", C.c_int, [C.c_int, _vp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp, C.c_int, C.c_int, _vp])
+_sig("b200rn_stem_conv_static", C.c_int, [C.c_int, _vp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp, C.c_int, C.c_int, _vp,
+                                          C.c_char_p, C.c_size_t])
 _sig("b200rn_fnv1a", C.c_uint32, [C.c_char_p, C.c_size_t])
 _sig("b200rn_ring_create", _vp, [C.c_int])
 _sig("b200rn_ring_destroy", None, [_vp])

@@ -621,3 +621,180 @@ cudaError_t umma_take_timeout_flag(unsigned int* flag) {
 }
 
 }  // namespace rn
+
+// =================================================================================================
+// b200rn_stem_conv_static -- the stem convolution for callers that must not allocate
+// =================================================================================================
+// Some hosts embed this library where device memory cannot be requested at call time: a worker
+// whose memory pool was sized and handed out at start-up, a latency-critical request thread for
+// which cudaMalloc's implicit device synchronisation is unacceptable, or a plugin slot whose
+// contract forbids the plugin to own device memory.  b200rn_stem_conv needs device scratch (the
+// zero-framed re-laid input, the packed filter bank, bias and input scale/shift) and takes it from
+// cudaMalloc.  This variant takes the same scratch from the fixed array below instead, so it calls
+// no cudaMalloc / cudaFree and no allocating routine of any library, on the host side either.
+//
+// The array costs kStaticScratchBytes (4 MiB + 58 KiB) of device memory on every GPU that loads
+// libb200rn.so, from load until the process exits, whether or not the entry point is ever called.
+// All calls on a device share it and it keeps whatever the previous call left behind, so every call
+// first zeroes the part of the frame it is about to use (the frame's borders are the convolution's
+// zero padding).  Two calls whose GPU work overlaps -- different host threads are serialised here by
+// a mutex and each call synchronises before returning, but another process-external stream or a
+// captured graph replay could still overlap -- would race on the array.
+namespace rn {
+namespace {
+constexpr size_t kStaticFrameBytes = size_t(4) << 20;                     // framed input images
+constexpr int kStaticMaxCout = 128;
+constexpr size_t kStaticWeightBytes = size_t(kStaticMaxCout) * 7 * 32 * 2;  // packed 16-bit filters
+constexpr size_t kStaticParamBytes = 1024;                                 // bias[128] + scale[4] + shift[4] (fp32)
+constexpr size_t kStaticScratchBytes = kStaticFrameBytes + kStaticWeightBytes + kStaticParamBytes;
+constexpr int kStaticMaxDevices = 64;
+}  // namespace
+}  // namespace rn
+
+// In host code this name is only a handle for the runtime, not a device address: passing it to a
+// kernel would fault (or silently touch host memory).  Host code below resolves the real address
+// with cudaGetSymbolAddress, once per device.
+static __device__ __align__(256) unsigned char g_static_scratch[rn::kStaticScratchBytes];
+
+namespace rn {
+namespace {
+
+std::mutex g_static_mu;
+unsigned char* g_static_dev_addr[kStaticMaxDevices] = {nullptr};   // resolved address per device ordinal
+// host-side staging, also static: nothing is allocated per call
+unsigned char g_static_host_weights[kStaticWeightBytes];
+float g_static_host_params[kStaticParamBytes / 4];
+
+CUresult encode_plain(CUtensorMap* m, DType dt, int rank, const void* base, const uint64_t* dims,
+                      const uint64_t* strides_bytes, const uint32_t* box, bool sw64) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return CUDA_ERROR_NOT_SUPPORTED;
+  cuuint64_t d[5]; cuuint64_t s[4]; cuuint32_t b[5], e[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
+  return fn(m, dt == DType::BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+            cuuint32_t(rank), const_cast<void*>(base), d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            sw64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+}
+
+// Same tile geometry, pipeline depth and tensor maps that umma_conv_plan_create builds for a stem
+// layer, written into a caller-provided (stack) object.
+bool fill_stem_plan(UmmaConvPlan& pl, DType dt, const ConvGeom& g, const void* frame, const void* w_packed,
+                    const float* d_bias, void* d_out, int relu) {
+  pl.dt = dt; pl.g = g; pl.stem = 1; pl.kb = 64; pl.block_n = 64;
+  UmmaParams& p = pl.p;
+  std::memset(&p, 0, sizeof p);
+  int bw = 0, bh = 0, bn = 0;
+  choose_patch(g.B, g.Ho, g.Wo, bw, bh, bn);
+  p.bw = bw; p.bh = bh; p.bn = bn;
+  p.tiles_w = (g.Wo + bw - 1) / bw;
+  p.tiles_h = (g.Ho + bh - 1) / bh;
+  const int tiles_n = (g.B + bn - 1) / bn;
+  p.n_tiles = g.Cout / 64;
+  p.rows = uint32_t(bw * bh * bn);
+  p.stem = 1; p.kw = 7; p.stride = 2; p.pad = 3; p.cblks = 1; p.num_k_iters = 7;
+  p.a_bytes = p.rows * 64u;
+  p.b_bytes = 64u * 64u;
+  p.has_out = 1; p.relu = relu; p.bias = d_bias;
+  const uint32_t stage_bytes = uint32_t(kTileM * 64 + 64 * 64);
+  const uint32_t staging = 2u * kChunkBytes;
+  const uint32_t tail_bytes = 3u * 64u * 4 + 8u * (2 * 8 + 2) + 16;
+  p.num_stages = 6;
+  pl.pipe_bytes = std::max(6u * stage_bytes, staging);
+  pl.smem_bytes = 1024u + pl.pipe_bytes + tail_bytes;
+  pl.grid = p.tiles_w * p.tiles_h * tiles_n * p.n_tiles;
+
+  const int Hp = stem_Hp(g.H), Wp = stem_Wp(g.W);
+  const uint64_t rowpitch = uint64_t(Wp) * 4 * 2;
+  uint64_t dims[5] = {32, uint64_t(g.Wo), 2, uint64_t(Hp / 2), uint64_t(g.B)};
+  uint64_t str[4] = {16, rowpitch, 2 * rowpitch, uint64_t(Hp) * rowpitch};
+  uint32_t box[5] = {32, uint32_t(bw), 1, uint32_t(bh), uint32_t(bn)};
+  if (encode_plain(&pl.tmA, dt, 5, frame, dims, str, box, true) != CUDA_SUCCESS) return false;
+  uint64_t wd[2] = {uint64_t(7 * 32), uint64_t(g.Cout)};
+  uint64_t ws[1] = {uint64_t(7 * 32) * 2};
+  uint32_t wb[2] = {32, 64};
+  if (encode_plain(&pl.tmW, dt, 2, w_packed, wd, ws, wb, true) != CUDA_SUCCESS) return false;
+  uint64_t od[4] = {uint64_t(g.Cout), uint64_t(g.Wo), uint64_t(g.Ho), uint64_t(g.B)};
+  uint64_t os[3] = {uint64_t(g.Cout) * 2, uint64_t(g.Wo) * g.Cout * 2, uint64_t(g.Ho) * g.Wo * g.Cout * 2};
+  uint32_t ob[4] = {64, uint32_t(bw), uint32_t(bh), uint32_t(bn)};
+  if (encode_plain(&pl.tmOut, dt, 4, d_out, od, os, ob, false) != CUDA_SUCCESS) return false;
+  pl.tmAct = pl.tmOut;    // unused by this launch, but passed by value: must be valid objects
+  pl.tmRes = pl.tmOut;
+  return true;
+}
+
+}  // namespace
+}  // namespace rn
+
+// Declared in include/b200rn.h.  Same arguments and same result as b200rn_stem_conv, plus an
+// optional buffer for the error text.  The FIRST call on each device resolves the scratch array's
+// device address (cudaGetSymbolAddress); make that first call outside any stream capture.
+extern "C" int b200rn_stem_conv_static(int dtype, const float* d_in_nchw, int B, int H, int W, const float* in_scale,
+                                       const float* in_shift, const float* w, const float* bias, int Cout, int relu,
+                                       void* d_out, char* err, size_t err_cap) {
+  using namespace rn;
+  auto fail = [&](int code, const char* fmt, long long a = 0, long long b = 0) {
+    if (err && err_cap) std::snprintf(err, err_cap, fmt, a, b);
+    return code;
+  };
+  if (!d_in_nchw || !w || !d_out || dtype < 1 || dtype > 2 || B <= 0 || H <= 0 || W <= 0)
+    return fail(1, "b200rn_stem_conv_static: bad argument");
+  if (H % 2) return fail(1, "b200rn_stem_conv_static: image height %lld must be even", H);
+  if (Cout <= 0 || Cout % 64 || Cout > kStaticMaxCout)
+    return fail(1, "b200rn_stem_conv_static: Cout %lld must be a multiple of 64 and at most %lld", Cout, kStaticMaxCout);
+  const int Hp = stem_Hp(H), Wp = stem_Wp(W);
+  const size_t frame_bytes = size_t(B) * Hp * Wp * 4 * 2;
+  if (frame_bytes > kStaticFrameBytes)
+    return fail(1, "b200rn_stem_conv_static: this batch needs %lld bytes of frame scratch, the static array holds %lld "
+                   "(use b200rn_stem_conv, which allocates, for larger batches)", (long long)frame_bytes, (long long)kStaticFrameBytes);
+
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  int dev = 0;
+  cudaError_t ce = cudaGetDevice(&dev);
+  if (ce != cudaSuccess) return fail(3, "b200rn_stem_conv_static: cudaGetDevice failed (%lld)", ce);
+  if (dev < 0 || dev >= kStaticMaxDevices) return fail(3, "b200rn_stem_conv_static: device ordinal %lld not supported", dev);
+  if (!g_static_dev_addr[dev]) {                 // one-time set-up for this device, with it current
+    void* p = nullptr;
+    ce = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (ce != cudaSuccess || !p) return fail(3, "b200rn_stem_conv_static: cudaGetSymbolAddress failed (%lld)", ce);
+    g_static_dev_addr[dev] = static_cast<unsigned char*>(p);
+  }
+  unsigned char* scratch = g_static_dev_addr[dev];
+  unsigned char* d_frame = scratch;
+  unsigned char* d_weights = scratch + kStaticFrameBytes;
+  float* d_params = reinterpret_cast<float*>(scratch + kStaticFrameBytes + kStaticWeightBytes);
+  float* d_bias = d_params;                       // [Cout]
+  float* d_scale = d_params + kStaticMaxCout;     // [4]
+  float* d_shift = d_scale + 4;                   // [4]
+
+  const DType dt = DType(dtype);
+  const int Ho = (H + 6 - 7) / 2 + 1, Wo = (W + 6 - 7) / 2 + 1;
+  ConvGeom g{B, H, W, 4, Ho, Wo, Cout, 7, 7, 2, 3};
+  // host staging (static): packed filters, then bias | scale | shift
+  umma_pack_weights(w, g, dt, 1, g_static_host_weights);
+  for (int c = 0; c < Cout; ++c) g_static_host_params[c] = bias ? bias[c] : 0.f;
+  for (int c = 0; c < 4; ++c) {
+    g_static_host_params[kStaticMaxCout + c] = (c < 3) ? (in_scale ? in_scale[c] : 1.f) : 0.f;
+    g_static_host_params[kStaticMaxCout + 4 + c] = (c < 3) ? (in_shift ? in_shift[c] : 0.f) : 0.f;
+  }
+  // the previous call's frame contents are still there: the borders must read as zero
+  if ((ce = cudaMemsetAsync(d_frame, 0, frame_bytes, 0)) != cudaSuccess)
+    return fail(3, "b200rn_stem_conv_static: cudaMemsetAsync failed (%lld)", ce);
+  if ((ce = cudaMemcpyAsync(d_weights, g_static_host_weights, umma_weight_bytes(g, 1), cudaMemcpyHostToDevice, 0)) != cudaSuccess)
+    return fail(3, "b200rn_stem_conv_static: filter upload failed (%lld)", ce);
+  if ((ce = cudaMemcpyAsync(d_params, g_static_host_params, (kStaticMaxCout + 8) * sizeof(float), cudaMemcpyHostToDevice, 0)) != cudaSuccess)
+    return fail(3, "b200rn_stem_conv_static: parameter upload failed (%lld)", ce);
+  if ((ce = launch_input_xform(d_in_nchw, d_frame, dt, B, 3, H, W, 4, Hp, Wp, 3, 3, d_scale, d_shift, 0, 0)) != cudaSuccess)
+    return fail(3, "b200rn_stem_conv_static: input re-layout launch failed (%lld)", ce);
+  UmmaConvPlan pl;
+  if (!fill_stem_plan(pl, dt, g, d_frame, d_weights, d_bias, d_out, relu))
+    return fail(3, "b200rn_stem_conv_static: tensor-map encoding failed");
+  const cudaError_t le = launch_conv_umma(&pl, 0);
+  const cudaError_t se = cudaDeviceSynchronize();
+  unsigned int flag = 0;
+  const cudaError_t fe = (se == cudaSuccess) ? umma_take_timeout_flag(&flag) : se;
+  if (le != cudaSuccess || se != cudaSuccess || fe != cudaSuccess || flag)
+    return fail(3, "b200rn_stem_conv_static: launch/sync error %lld, barrier timeout %lld", (long long)(le ? le : (se ? se : fe)), flag);
+  return 0;
+}

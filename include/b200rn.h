@@ -133,6 +133,26 @@ int b200rn_conv2d(int dtype, const void* d_in, int B, int H, int W, int Cin, con
 int b200rn_stem_conv(int dtype, const float* d_in_nchw, int B, int H, int W, const float* in_scale,
                      const float* in_shift, const float* w, const float* bias, int Cout, int relu, void* d_out);
 
+/* No counterpart in the reference.  The same stem convolution as b200rn_stem_conv for callers that
+ * cannot allocate device memory when they call in (a worker whose device pool was carved up at start-up,
+ * a request thread that cannot afford cudaMalloc's device-wide synchronisation, a plugin host that
+ * forbids plugins to own device memory).  All scratch -- the zero-framed re-laid input, the packed
+ * filters, bias and input scale/shift -- lives in ONE fixed array inside the library
+ * (B200RN_STATIC_SCRATCH_BYTES of device memory on every GPU that loads libb200rn.so, held until the
+ * process exits), so the call performs no cudaMalloc/cudaFree and no heap allocation.
+ * Limits: B * (H+6) * round_up(W+8, 8) * 8 bytes must fit in B200RN_STATIC_FRAME_BYTES (nine 224x224
+ * images), Cout must be 64 or 128, H even; anything larger is refused with a message (use
+ * b200rn_stem_conv).  The first call on each device looks up the array's device address; make that first
+ * call before any stream capture begins.  Every call shares the array and starts by clearing the part it
+ * uses; calls whose GPU work overlaps would race on it (calls through this entry point are serialised and
+ * synchronous, so that can only happen if the caller overlaps it with a replayed capture of itself).
+ * err (optional, err_cap bytes) receives the failure text.  Returns 0 on success. */
+#define B200RN_STATIC_FRAME_BYTES (4u << 20)
+#define B200RN_STATIC_SCRATCH_BYTES ((4u << 20) + 57344u + 1024u)
+int b200rn_stem_conv_static(int dtype, const float* d_in_nchw, int B, int H, int W, const float* in_scale,
+                            const float* in_shift, const float* w, const float* bias, int Cout, int relu,
+                            void* d_out, char* err, size_t err_cap);
+
 /* ---- request routing and cache keys (bit-exact restatements used by the serving shell) ----
  * Replaces ConsistentHash (include/consistent_hash.h, src/consistent_hash.cpp:6-45) and
  * VectorHash (include/lru_cache.h:84-96). */
