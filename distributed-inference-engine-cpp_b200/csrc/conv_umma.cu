@@ -38,7 +38,7 @@ constexpr int kChunkBytes = kTileM * 128;  // one 64-channel output chunk of a t
 struct UmmaParams {
   int num_k_iters, cblks, kw, stride, pad, stem;
   int bw, bh, bn, tiles_w, tiles_h;
-  int n_tiles, num_stages;
+  int n_tiles, num_stages, total_tiles, raw_bufs;
   int has_res, has_out, has_act, relu, act_relu;
   uint32_t a_bytes, b_bytes, rows;
   const float* bias;
@@ -188,43 +188,66 @@ template <> __device__ __forceinline__ float2 unpack2<__half>(uint32_t u) {
 }
 
 // ---- the kernel -------------------------------------------------------------------------------
+// Persistent: one CTA per SM walks the tile list (tile = blockIdx.x + i*gridDim.x, N-tile fastest so
+// CTAs that share an A tile run side by side).  The accumulator is double-buffered in TMEM
+// (2 x BLOCK_N columns), so the epilogue of tile i overlaps the MMAs of tile i+1; the residual /
+// raw-output staging buffer is double-buffered in shared memory for the same reason.
+//
 // Dynamic shared memory (1024-byte aligned):
-//   [pipeline: num_stages x (A tile | B tile)]   reused as output staging once the MMAs are done
-//   [residual: BLOCK_N/64 x 16 KB]               only when has_res; raw output is staged in place
+//   [pipeline: num_stages x (A tile | B tile)]
+//   [rawbuf:   raw_bufs (1|2) x BLOCK_N/64 x 16 KB]   residual lands here by TMA; the raw output is staged in place
+//   [actbuf:   BLOCK_N/64 x 16 KB]       only when has_act
 //   [params:   3 x BLOCK_N floats][barriers][tmem slot]
+struct TileCoord { int w0, h0, n0, col0, n_tile; };
+
+__device__ __forceinline__ TileCoord decode_tile(const UmmaParams& p, int tile, int block_n) {
+  TileCoord t;
+  t.n_tile = tile % p.n_tiles;
+  int mt = tile / p.n_tiles;
+  const int tw = mt % p.tiles_w; mt /= p.tiles_w;
+  const int th = mt % p.tiles_h;
+  const int tn = mt / p.tiles_h;
+  t.w0 = tw * p.bw; t.h0 = th * p.bh; t.n0 = tn * p.bn;
+  t.col0 = t.n_tile * block_n;
+  return t;
+}
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
 template <typename T, int BLOCK_N, int KB>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
-                 const __grid_constant__ CUtensorMap tmAct, const UmmaParams p, const uint32_t pipe_bytes) {
+                 const __grid_constant__ CUtensorMap tmAct, const UmmaParams p) {
   constexpr int kChunks = BLOCK_N / 64;
   constexpr int kMmaPerBlock = KB / 32;        // UMMA_K = 16 elements = 32 bytes
   constexpr uint32_t A_BYTES = kTileM * KB;
   constexpr uint32_t B_BYTES = BLOCK_N * KB;
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr uint32_t RAW_BYTES = kChunks * kChunkBytes;   // one tile's raw / residual staging
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int S = p.num_stages;
   uint8_t* pipe = smem;
-  uint8_t* resbuf = smem + pipe_bytes;
-  uint8_t* tail = resbuf + (p.has_res ? kChunks * kChunkBytes : 0);
+  uint8_t* rawbuf = pipe + S * STAGE_BYTES;
+  uint8_t* actbuf = rawbuf + ((p.has_out || p.has_res) ? p.raw_bufs * RAW_BYTES : 0);
+  uint8_t* tail = actbuf + (p.has_act ? RAW_BYTES : 0);
   float* s_bias = reinterpret_cast<float*>(tail);
   float* s_scale = s_bias + BLOCK_N;
   float* s_shift = s_scale + BLOCK_N;
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_shift + BLOCK_N);
-  // bars[0..S) full, bars[S..2S) empty, bars[2S] tmem_full, bars[2S+1] res_full
-  const int S = p.num_stages;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 2);
+  uint64_t* full_bar = bars;                  // [S]  TMA -> MMA
+  uint64_t* empty_bar = bars + S;             // [S]  MMA -> TMA
+  uint64_t* tmem_full = bars + 2 * S;         // [2]  MMA -> epilogue
+  uint64_t* tmem_empty = tmem_full + 2;       // [2]  epilogue -> MMA (128 arrivals)
+  uint64_t* res_full = tmem_empty + 2;        // [2]  TMA -> epilogue
+  uint64_t* res_empty = res_full + 2;         // [2]  epilogue -> TMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tile = blockIdx.x;
-  const int n_tile = tile % p.n_tiles;
-  int mt = tile / p.n_tiles;
-  const int tw = mt % p.tiles_w; mt /= p.tiles_w;
-  const int th = mt % p.tiles_h;
-  const int tn = mt / p.tiles_h;
-  const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
-  const int col0 = n_tile * BLOCK_N;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
@@ -233,21 +256,18 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (p.has_out) prefetch_tmap(&tmOut);
     if (p.has_act) prefetch_tmap(&tmAct);
     for (int i = 0; i < S; ++i) {
-      mbar_init(smem_u32(&bars[i]), 1);
-      mbar_init(smem_u32(&bars[S + i]), 1);
+      mbar_init(smem_u32(&full_bar[i]), 1);
+      mbar_init(smem_u32(&empty_bar[i]), 1);
     }
-    mbar_init(smem_u32(&bars[2 * S]), 1);
-    mbar_init(smem_u32(&bars[2 * S + 1]), 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&tmem_full[i]), 1);
+      mbar_init(smem_u32(&tmem_empty[i]), 128);
+      mbar_init(smem_u32(&res_full[i]), 1);
+      mbar_init(smem_u32(&res_empty[i]), 1);
+    }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), BLOCK_N);
-  if (warp >= 2) {
-    for (int i = threadIdx.x - 64; i < BLOCK_N; i += 128) {
-      s_bias[i] = __ldg(p.bias + col0 + i);
-      s_scale[i] = p.has_act ? __ldg(p.act_scale + col0 + i) : 1.f;
-      s_shift[i] = p.has_act ? __ldg(p.act_shift + col0 + i) : 0.f;
-    }
-  }
+  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * BLOCK_N);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -256,29 +276,37 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0) {
     // ===== TMA producer =====
     if (elect_one()) {
-      if (p.has_res) {
-        const uint32_t rb = smem_u32(&bars[2 * S + 1]);
-        mbar_expect_tx(rb, p.rows * 128u * kChunks);
-#pragma unroll
-        for (int c = 0; c < kChunks; ++c)
-          tma_load_4d(smem_u32(resbuf + c * kChunkBytes), &tmRes, rb, col0 + c * 64, w0, h0, n0);
-      }
       int stage = 0;
       uint32_t phase = 0;
-      for (int it = 0; it < p.num_k_iters; ++it) {
-        mbar_wait(smem_u32(&bars[S + stage]), phase ^ 1);
-        const uint32_t fb = smem_u32(&bars[stage]);
-        const uint32_t a_dst = smem_u32(pipe + stage * STAGE_BYTES);
-        mbar_expect_tx(fb, p.a_bytes + p.b_bytes);
-        if (p.stem) {
-          tma_load_5d(a_dst, &tmA, fb, 0, w0, it & 1, h0 + (it >> 1), n0);
-        } else {
-          const int tap = it / p.cblks, cb = it - tap * p.cblks;
-          const int ky = tap / p.kw, kx = tap - ky * p.kw;
-          tma_load_4d(a_dst, &tmA, fb, cb * 64, w0 * p.stride - p.pad + kx, h0 * p.stride - p.pad + ky, n0);
+      int i = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++i) {
+        const TileCoord tc = decode_tile(p, tile, BLOCK_N);
+        for (int it = 0; it < p.num_k_iters; ++it) {
+          mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
+          const uint32_t fb = smem_u32(&full_bar[stage]);
+          const uint32_t a_dst = smem_u32(pipe + stage * STAGE_BYTES);
+          mbar_expect_tx(fb, p.a_bytes + p.b_bytes);
+          if (p.stem) {
+            tma_load_5d(a_dst, &tmA, fb, 0, tc.w0, it & 1, tc.h0 + (it >> 1), tc.n0);
+          } else {
+            const int tap = it / p.cblks, cb = it - tap * p.cblks;
+            const int ky = tap / p.kw, kx = tap - ky * p.kw;
+            tma_load_4d(a_dst, &tmA, fb, cb * 64, tc.w0 * p.stride - p.pad + kx, tc.h0 * p.stride - p.pad + ky, tc.n0);
+          }
+          tma_load_2d(a_dst + A_BYTES, &tmW, fb, it * (KB / 2), tc.col0);
+          if (++stage == S) { stage = 0; phase ^= 1; }
         }
-        tma_load_2d(a_dst + A_BYTES, &tmW, fb, it * (KB / 2), col0);
-        if (++stage == S) { stage = 0; phase ^= 1; }
+        if (p.has_res) {
+          // after this tile's operands, so a late epilogue never delays the main loop
+          const int rb = (p.raw_bufs == 2) ? (i & 1) : 0;
+          const uint32_t rpar = (p.raw_bufs == 2) ? ((i >> 1) & 1) : (i & 1);
+          mbar_wait(smem_u32(&res_empty[rb]), rpar ^ 1);
+          const uint32_t bar = smem_u32(&res_full[rb]);
+          mbar_expect_tx(bar, p.rows * 128u * kChunks);
+#pragma unroll
+          for (int c = 0; c < kChunks; ++c)
+            tma_load_4d(smem_u32(rawbuf + rb * RAW_BYTES + c * kChunkBytes), &tmRes, bar, tc.col0 + c * 64, tc.w0, tc.h0, tc.n0);
+        }
       }
     }
   } else if (warp == 1) {
@@ -286,88 +314,123 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr uint32_t idesc = make_idesc<T, BLOCK_N>();
     int stage = 0;
     uint32_t phase = 0;
-    for (int it = 0; it < p.num_k_iters; ++it) {
-      mbar_wait(smem_u32(&bars[stage]), phase);
+    int i = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++i) {
+      const int buf = i & 1;
+      mbar_wait(smem_u32(&tmem_empty[buf]), ((i >> 1) & 1) ^ 1);   // epilogue drained this accumulator
       tc_fence_after();
-      if (elect_one()) {
-        const uint32_t a_addr = smem_u32(pipe + stage * STAGE_BYTES);
-        const uint32_t b_addr = a_addr + A_BYTES;
+      const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
+      for (int it = 0; it < p.num_k_iters; ++it) {
+        mbar_wait(smem_u32(&full_bar[stage]), phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a_addr = smem_u32(pipe + stage * STAGE_BYTES);
+          const uint32_t b_addr = a_addr + A_BYTES;
 #pragma unroll
-        for (int k = 0; k < kMmaPerBlock; ++k) {
-          const uint64_t da = make_smem_desc<KB>(a_addr + k * 32);
-          const uint64_t db = make_smem_desc<KB>(b_addr + k * 32);
-          umma_f16(tmem_base, da, db, idesc, (it | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < kMmaPerBlock; ++k) {
+            const uint64_t da = make_smem_desc<KB>(a_addr + k * 32);
+            const uint64_t db = make_smem_desc<KB>(b_addr + k * 32);
+            umma_f16(tmem_d, da, db, idesc, (it | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(smem_u32(&empty_bar[stage]));                               // frees the smem slot
+          if (it == p.num_k_iters - 1) umma_commit(smem_u32(&tmem_full[buf]));     // accumulator complete
         }
-        umma_commit(smem_u32(&bars[S + stage]));                              // frees the smem slot
-        if (it == p.num_k_iters - 1) umma_commit(smem_u32(&bars[2 * S]));      // accumulator complete
+        __syncwarp();
+        if (++stage == S) { stage = 0; phase ^= 1; }
       }
-      __syncwarp();
-      if (++stage == S) { stage = 0; phase ^= 1; }
     }
   } else {
     // ===== epilogue: 4 warps, thread = one output pixel (TMEM lane) =====
     const int q = warp & 3;                 // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;
-    mbar_wait(smem_u32(&bars[2 * S]), 0);
-    tc_fence_after();
-    if (p.has_res) mbar_wait(smem_u32(&bars[2 * S + 1]), 0);
     const int sw = row & 7;
-#pragma unroll 1
-    for (int c = 0; c < kChunks; ++c) {
-      uint32_t acc[64];
-      {
-        uint32_t (&lo)[32] = *reinterpret_cast<uint32_t (*)[32]>(&acc[0]);
-        uint32_t (&hi)[32] = *reinterpret_cast<uint32_t (*)[32]>(&acc[32]);
-        const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(c * 64);
-        tmem_ld_32x32b_x32(taddr, lo);
-        tmem_ld_32x32b_x32(taddr + 32, hi);
-        tmem_ld_wait();
-      }
-      uint8_t* raw_stage = p.has_res ? (resbuf + c * kChunkBytes) : (pipe + (2 * c) * kChunkBytes);
-      uint8_t* act_stage = pipe + (2 * c + 1) * kChunkBytes;
-      uint4* raw_row = reinterpret_cast<uint4*>(raw_stage + row * 128);
-      uint4* act_row = reinterpret_cast<uint4*>(act_stage + row * 128);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {           // 8 channels (16 bytes) at a time
-        float v[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          v[i] = __uint_as_float(acc[j * 8 + i]) + s_bias[c * 64 + j * 8 + i];
-          if (p.relu) v[i] = fmaxf(v[i], 0.f);
-        }
-        const int slot = j ^ sw;              // SWIZZLE_128B: 16-byte chunk index XOR (row mod 8)
-        if (p.has_res) {
-          const uint4 r = raw_row[slot];
-          const float2 r0 = unpack2<T>(r.x), r1 = unpack2<T>(r.y), r2 = unpack2<T>(r.z), r3 = unpack2<T>(r.w);
-          v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
-          v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
-        }
-        if (p.has_out)
-          raw_row[slot] = make_uint4(pack2<T>(v[0], v[1]), pack2<T>(v[2], v[3]), pack2<T>(v[4], v[5]), pack2<T>(v[6], v[7]));
-        if (p.has_act) {
-          float a[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            a[i] = fmaf(s_scale[c * 64 + j * 8 + i], v[i], s_shift[c * 64 + j * 8 + i]);
-            if (p.act_relu) a[i] = fmaxf(a[i], 0.f);
-          }
-          act_row[slot] = make_uint4(pack2<T>(a[0], a[1]), pack2<T>(a[2], a[3]), pack2<T>(a[4], a[5]), pack2<T>(a[6], a[7]));
+    const int et = threadIdx.x - 64;        // 0..127
+    const bool store_thread = (warp == 2 && lane == 0);
+    int cur_ntile = -1;
+    int i = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++i) {
+      const TileCoord tc = decode_tile(p, tile, BLOCK_N);
+      const int buf = i & 1;
+      const uint32_t par = (i >> 1) & 1;
+      if (tc.n_tile != cur_ntile) {         // per-channel parameters of this N tile
+        cur_ntile = tc.n_tile;
+        for (int k = et; k < BLOCK_N; k += 128) {
+          s_bias[k] = __ldg(p.bias + tc.col0 + k);
+          s_scale[k] = p.has_act ? __ldg(p.act_scale + tc.col0 + k) : 1.f;
+          s_shift[k] = p.has_act ? __ldg(p.act_shift + tc.col0 + k) : 0.f;
         }
       }
-      fence_proxy_async_smem();
+      if (store_thread && i > 0) {
+        tma_store_wait_read();              // previous tile's stores have read their staging buffers
+        if (p.has_res) mbar_arrive(smem_u32(&res_empty[(p.raw_bufs == 2) ? ((i - 1) & 1) : 0]));
+      }
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (warp == 2 && lane == 0) {
-        if (p.has_out) tma_store_4d(&tmOut, smem_u32(raw_stage), col0 + c * 64, w0, h0, n0);
-        if (p.has_act) tma_store_4d(&tmAct, smem_u32(act_stage), col0 + c * 64, w0, h0, n0);
-        tma_store_commit();
+      mbar_wait(smem_u32(&tmem_full[buf]), par);
+      tc_fence_after();
+      const int rb = (p.raw_bufs == 2) ? (i & 1) : 0;
+      if (p.has_res) mbar_wait(smem_u32(&res_full[rb]), (p.raw_bufs == 2) ? par : uint32_t(i & 1));
+      uint8_t* raw_tile = rawbuf + rb * RAW_BYTES;
+#pragma unroll 1
+      for (int c = 0; c < kChunks; ++c) {
+        uint32_t acc[64];
+        {
+          uint32_t (&lo)[32] = *reinterpret_cast<uint32_t (*)[32]>(&acc[0]);
+          uint32_t (&hi)[32] = *reinterpret_cast<uint32_t (*)[32]>(&acc[32]);
+          const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(buf * BLOCK_N + c * 64);
+          tmem_ld_32x32b_x32(taddr, lo);
+          tmem_ld_32x32b_x32(taddr + 32, hi);
+          tmem_ld_wait();
+        }
+        if (c == kChunks - 1) {             // accumulator fully read: hand it back to the MMA warp
+          tc_fence_before();
+          mbar_arrive(smem_u32(&tmem_empty[buf]));
+        }
+        uint8_t* raw_stage = raw_tile + c * kChunkBytes;
+        uint8_t* act_stage = actbuf + c * kChunkBytes;
+        uint4* raw_row = reinterpret_cast<uint4*>(raw_stage + row * 128);
+        uint4* act_row = reinterpret_cast<uint4*>(act_stage + row * 128);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {         // 8 channels (16 bytes) at a time
+          float v[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            v[k] = __uint_as_float(acc[j * 8 + k]) + s_bias[c * 64 + j * 8 + k];
+            if (p.relu) v[k] = fmaxf(v[k], 0.f);
+          }
+          const int slot = j ^ sw;            // SWIZZLE_128B: 16-byte chunk index XOR (row mod 8)
+          if (p.has_res) {
+            const uint4 r = raw_row[slot];
+            const float2 r0 = unpack2<T>(r.x), r1 = unpack2<T>(r.y), r2 = unpack2<T>(r.z), r3 = unpack2<T>(r.w);
+            v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
+            v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
+          }
+          if (p.has_out)
+            raw_row[slot] = make_uint4(pack2<T>(v[0], v[1]), pack2<T>(v[2], v[3]), pack2<T>(v[4], v[5]), pack2<T>(v[6], v[7]));
+          if (p.has_act) {
+            float a[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              a[k] = fmaf(s_scale[c * 64 + j * 8 + k], v[k], s_shift[c * 64 + j * 8 + k]);
+              if (p.act_relu) a[k] = fmaxf(a[k], 0.f);
+            }
+            act_row[slot] = make_uint4(pack2<T>(a[0], a[1]), pack2<T>(a[2], a[3]), pack2<T>(a[4], a[5]), pack2<T>(a[6], a[7]));
+          }
+        }
+        fence_proxy_async_smem();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (store_thread) {
+          if (p.has_out) tma_store_4d(&tmOut, smem_u32(raw_stage), tc.col0 + c * 64, tc.w0, tc.h0, tc.n0);
+          if (p.has_act) tma_store_4d(&tmAct, smem_u32(act_stage), tc.col0 + c * 64, tc.w0, tc.h0, tc.n0);
+          tma_store_commit();
+        }
       }
     }
-    if (warp == 2 && lane == 0) tma_store_wait_read();
+    if (store_thread) tma_store_wait_read();
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, BLOCK_N);
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
 }
 
 // ---- host side --------------------------------------------------------------------------------
@@ -434,7 +497,7 @@ struct UmmaConvPlan {
   int block_n, kb;
   UmmaParams p;
   CUtensorMap tmA, tmW, tmRes, tmOut, tmAct;
-  uint32_t pipe_bytes, smem_bytes;
+  uint32_t smem_bytes;
   int grid;
 };
 
@@ -497,6 +560,76 @@ static void choose_patch(int B, int Ho, int Wo, int& bw, int& bh, int& bn) {
     }
 }
 
+static int sm_count() {
+  static int n[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return 148;
+  if (!n[dev]) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    n[dev] = v;
+  }
+  return n[dev];
+}
+
+// Tile geometry, pipeline depth and launch shape of one layer at one batch size.  Needs pl.dt, pl.g,
+// pl.stem and the has_* flags of pl.p; fills everything else except the tensor maps.
+static void plan_geometry(UmmaConvPlan& pl) {
+  const ConvGeom& g = pl.g;
+  UmmaParams& p = pl.p;
+  const int stem_mode = pl.stem;
+  pl.kb = stem_mode ? 64 : 128;
+  int bw = 0, bh = 0, bn = 0;
+  choose_patch(g.B, g.Ho, g.Wo, bw, bh, bn);
+  p.bw = bw; p.bh = bh; p.bn = bn;
+  p.tiles_w = (g.Wo + bw - 1) / bw;
+  p.tiles_h = (g.Ho + bh - 1) / bh;
+  const int tiles_n = (g.B + bn - 1) / bn;
+  const int m_tiles = p.tiles_w * p.tiles_h * tiles_n;
+  const int sms = sm_count();
+  // N-tile width: minimise (rounds over the SMs) x (operand bytes staged per K block), i.e. the
+  // shared-memory fill traffic per SM, among the widths that divide Cout and leave >= 3 stages.
+  const uint32_t budget = 227u * 1024;
+  auto fixed_bytes = [&](int bn, int nb) {
+    const uint32_t raw_bytes = uint32_t(bn / 64) * kChunkBytes;
+    return 1024u + ((p.has_out || p.has_res) ? uint32_t(nb) * raw_bytes : 0u) + (p.has_act ? raw_bytes : 0u) +
+           3u * uint32_t(bn) * 4 + 8u * (2 * 8 + 8) + 64;
+  };
+  auto stage_bytes_of = [&](int bn) { return uint32_t(kTileM * pl.kb + bn * pl.kb); };
+  int best_bn = 64;
+  long best_cost = -1;
+  for (int bn_c : {64, 128, 256}) {
+    if (g.Cout % bn_c) continue;
+    if (stem_mode && bn_c != 64) continue;
+    const int nb_c = p.has_res ? 2 : 1;
+    const uint32_t fx = std::min(fixed_bytes(bn_c, nb_c), fixed_bytes(bn_c, 1));
+    if (bn_c > 64 && (budget < fx || (budget - fx) / stage_bytes_of(bn_c) < 3)) continue;
+    const long tiles = long(m_tiles) * (g.Cout / bn_c);
+    const long cost = ((tiles + sms - 1) / sms) * long(kTileM + bn_c);
+    if (best_cost < 0 || cost <= best_cost) { best_cost = cost; best_bn = bn_c; }
+  }
+  pl.block_n = best_bn;
+  p.n_tiles = g.Cout / pl.block_n;
+  p.total_tiles = m_tiles * p.n_tiles;
+  p.rows = uint32_t(bw * bh * bn);
+  p.stem = stem_mode; p.kw = g.kw; p.stride = g.stride; p.pad = g.pad;
+  p.cblks = stem_mode ? 1 : g.Cin / 64;
+  p.num_k_iters = stem_mode ? 7 : g.kh * g.kw * p.cblks;
+  p.a_bytes = p.rows * uint32_t(pl.kb);
+  p.b_bytes = uint32_t(pl.block_n * pl.kb);
+  const uint32_t stage_bytes = stage_bytes_of(pl.block_n);
+  // double-buffer the residual/raw staging when a residual is prefetched and it still leaves 3 stages
+  p.raw_bufs = (p.has_res && budget > fixed_bytes(pl.block_n, 2) &&
+                (budget - fixed_bytes(pl.block_n, 2)) / stage_bytes >= 3) ? 2 : 1;
+  const uint32_t fixed = fixed_bytes(pl.block_n, p.raw_bufs);
+  int stages = int((budget - fixed) / stage_bytes);
+  stages = std::max(2, std::min(stages, 8));
+  p.num_stages = stages;
+  pl.smem_bytes = fixed + uint32_t(stages) * stage_bytes;
+  pl.grid = std::min(p.total_tiles, sms);
+}
+
 template <typename T, int BLOCK_N, int KB>
 static cudaError_t launch_inst(const UmmaConvPlan* pl, cudaStream_t s) {
   auto kern = conv_umma_kernel<T, BLOCK_N, KB>;
@@ -508,7 +641,7 @@ static cudaError_t launch_inst(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  kern<<<pl->grid, kThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->p, pl->pipe_bytes);
+  kern<<<pl->grid, kThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->p);
   return cudaGetLastError();
 }
 
@@ -516,7 +649,8 @@ cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
   const bool bf = pl->dt == DType::BF16;
   if (pl->kb == 64) return bf ? launch_inst<__nv_bfloat16, 64, 64>(pl, s) : launch_inst<__half, 64, 64>(pl, s);
   if (pl->block_n == 64) return bf ? launch_inst<__nv_bfloat16, 64, 128>(pl, s) : launch_inst<__half, 64, 128>(pl, s);
-  return bf ? launch_inst<__nv_bfloat16, 128, 128>(pl, s) : launch_inst<__half, 128, 128>(pl, s);
+  if (pl->block_n == 128) return bf ? launch_inst<__nv_bfloat16, 128, 128>(pl, s) : launch_inst<__half, 128, 128>(pl, s);
+  return bf ? launch_inst<__nv_bfloat16, 256, 128>(pl, s) : launch_inst<__half, 256, 128>(pl, s);
 }
 
 UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in, const void* w_packed,
@@ -530,42 +664,14 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   if (!umma_conv_supported(g, stem_mode, why, sizeof why)) return failmsg(why);
   auto pl = new UmmaConvPlan();
   pl->dt = dt; pl->g = g; pl->stem = stem_mode;
-  pl->kb = stem_mode ? 64 : 128;
-  pl->block_n = (stem_mode || g.Cout % 128) ? 64 : 128;
   UmmaParams& p = pl->p;
   std::memset(&p, 0, sizeof p);
-  int bw = 0, bh = 0, bn = 0;
-  choose_patch(g.B, g.Ho, g.Wo, bw, bh, bn);
-  p.bw = bw; p.bh = bh; p.bn = bn;
-  p.tiles_w = (g.Wo + bw - 1) / bw;
-  p.tiles_h = (g.Ho + bh - 1) / bh;
-  int tiles_n = (g.B + bn - 1) / bn;
-  p.n_tiles = g.Cout / pl->block_n;
-  p.rows = uint32_t(bw * bh * bn);
-  p.stem = stem_mode; p.kw = g.kw; p.stride = g.stride; p.pad = g.pad;
-  p.cblks = stem_mode ? 1 : g.Cin / 64;
-  p.num_k_iters = stem_mode ? 7 : g.kh * g.kw * p.cblks;
-  p.a_bytes = p.rows * uint32_t(pl->kb);
-  p.b_bytes = uint32_t(pl->block_n * pl->kb);
   p.has_res = e.residual != nullptr; p.has_out = e.out != nullptr; p.has_act = e.out_act != nullptr;
   p.relu = e.relu; p.act_relu = e.act_relu;
   p.bias = e.bias; p.act_scale = e.act_scale; p.act_shift = e.act_shift;
   if (!p.has_out && !p.has_act) { delete pl; return failmsg("conv with no output"); }
-
-  const uint32_t stage_bytes = uint32_t(kTileM * pl->kb + pl->block_n * pl->kb);
-  const int chunks = pl->block_n / 64;
-  const uint32_t staging = uint32_t(2 * chunks) * kChunkBytes;
-  const uint32_t res_bytes = p.has_res ? uint32_t(chunks) * kChunkBytes : 0;
-  const uint32_t tail_bytes = 3u * uint32_t(pl->block_n) * 4 + 8u * (2 * 8 + 2) + 16;
-  // deepest pipeline that still lets two CTAs share an SM (2 x ~113 KB), at least 2, at most 6
-  int stages = 6;
-  auto total = [&](int s) { return 1024u + std::max(uint32_t(s) * stage_bytes, staging) + res_bytes + tail_bytes; };
-  while (stages > 2 && total(stages) > 113u * 1024) --stages;
-  if (stages > p.num_k_iters) stages = std::max(1, p.num_k_iters);
-  p.num_stages = stages;
-  pl->pipe_bytes = std::max(uint32_t(stages) * stage_bytes, staging);
-  pl->smem_bytes = 1024u + pl->pipe_bytes + res_bytes + tail_bytes;
-  pl->grid = p.tiles_w * p.tiles_h * tiles_n * p.n_tiles;
+  plan_geometry(*pl);
+  const int bw = p.bw, bh = p.bh, bn = p.bn;
 
   std::string msg;
   bool ok = true;
@@ -682,28 +788,12 @@ CUresult encode_plain(CUtensorMap* m, DType dt, int rank, const void* base, cons
 // layer, written into a caller-provided (stack) object.
 bool fill_stem_plan(UmmaConvPlan& pl, DType dt, const ConvGeom& g, const void* frame, const void* w_packed,
                     const float* d_bias, void* d_out, int relu) {
-  pl.dt = dt; pl.g = g; pl.stem = 1; pl.kb = 64; pl.block_n = 64;
+  pl.dt = dt; pl.g = g; pl.stem = 1;
   UmmaParams& p = pl.p;
   std::memset(&p, 0, sizeof p);
-  int bw = 0, bh = 0, bn = 0;
-  choose_patch(g.B, g.Ho, g.Wo, bw, bh, bn);
-  p.bw = bw; p.bh = bh; p.bn = bn;
-  p.tiles_w = (g.Wo + bw - 1) / bw;
-  p.tiles_h = (g.Ho + bh - 1) / bh;
-  const int tiles_n = (g.B + bn - 1) / bn;
-  p.n_tiles = g.Cout / 64;
-  p.rows = uint32_t(bw * bh * bn);
-  p.stem = 1; p.kw = 7; p.stride = 2; p.pad = 3; p.cblks = 1; p.num_k_iters = 7;
-  p.a_bytes = p.rows * 64u;
-  p.b_bytes = 64u * 64u;
   p.has_out = 1; p.relu = relu; p.bias = d_bias;
-  const uint32_t stage_bytes = uint32_t(kTileM * 64 + 64 * 64);
-  const uint32_t staging = 2u * kChunkBytes;
-  const uint32_t tail_bytes = 3u * 64u * 4 + 8u * (2 * 8 + 2) + 16;
-  p.num_stages = 6;
-  pl.pipe_bytes = std::max(6u * stage_bytes, staging);
-  pl.smem_bytes = 1024u + pl.pipe_bytes + tail_bytes;
-  pl.grid = p.tiles_w * p.tiles_h * tiles_n * p.n_tiles;
+  plan_geometry(pl);
+  const int bw = p.bw, bh = p.bh, bn = p.bn;
 
   const int Hp = stem_Hp(g.H), Wp = stem_Wp(g.W);
   const uint64_t rowpitch = uint64_t(Wp) * 4 * 2;

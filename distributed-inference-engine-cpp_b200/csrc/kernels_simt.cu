@@ -63,6 +63,26 @@ template <> __device__ inline float from_float<float>(float f) { return f; }
 template <> __device__ inline __nv_bfloat16 from_float<__nv_bfloat16>(float f) { return __float2bfloat16_rn(f); }
 template <> __device__ inline __half from_float<__half>(float f) { return __float2half_rn(f); }
 
+// one pixel = 4 channels: 8 bytes (16-bit types) or 16 bytes (fp32), naturally aligned
+template <typename T> __device__ inline void store_pixel4(T* dst, const float (&v)[4]);
+template <> __device__ inline void store_pixel4<float>(float* dst, const float (&v)[4]) {
+  *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+}
+template <> __device__ inline void store_pixel4<__nv_bfloat16>(__nv_bfloat16* dst, const float (&v)[4]) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&a);
+  u.y = *reinterpret_cast<uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(dst) = u;
+}
+template <> __device__ inline void store_pixel4<__half>(__half* dst, const float (&v)[4]) {
+  __half2 a = __floats2half2_rn(v[0], v[1]), b = __floats2half2_rn(v[2], v[3]);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&a);
+  u.y = *reinterpret_cast<uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(dst) = u;
+}
+
 inline int grid_for(int64_t threads, int block) {
   int64_t g = (threads + block - 1) / block;
   if (g < 1) g = 1;
@@ -70,7 +90,42 @@ inline int grid_for(int64_t threads, int block) {
 }
 
 // ---- input re-layout ------------------------------------------------------------------------
-// One thread per pixel: reads C planes (coalesced along W), writes Cpad contiguous channels.
+// One thread per 4 consecutive pixels of a row: three float4 plane reads (coalesced along W), one
+// 32-byte (16-bit types) or 64-byte (fp32) store of 4 pixels x 4 channels.  Requires W % 4 == 0,
+// Cpad == 4 and C <= 4; anything else takes the scalar kernel below.
+template <typename T>
+__global__ void input_xform_vec4_kernel(const float* __restrict__ in, T* __restrict__ out, int B, int C, int H, int W,
+                                        int Hp, int Wp, int off_h, int off_w, const float* __restrict__ scale,
+                                        const float* __restrict__ shift, int relu) {
+  const int W4 = W >> 2;
+  int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  int64_t total = int64_t(B) * H * W4;
+  if (idx >= total) return;
+  int w = int(idx % W4) * 4;
+  int h = int((idx / W4) % H);
+  int b = int(idx / (int64_t(W4) * H));
+  float v[4][4];   // [pixel][channel]
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    float sc = 0.f, sh = 0.f;
+    if (c < C) {
+      x = __ldg(reinterpret_cast<const float4*>(in + ((int64_t(b) * C + c) * H + h) * W + w));
+      sc = __ldg(scale + c); sh = __ldg(shift + c);
+    }
+    v[0][c] = fmaf(sc, x.x, sh); v[1][c] = fmaf(sc, x.y, sh); v[2][c] = fmaf(sc, x.z, sh); v[3][c] = fmaf(sc, x.w, sh);
+    if (relu) {
+#pragma unroll
+      for (int px = 0; px < 4; ++px) v[px][c] = fmaxf(v[px][c], 0.f);
+    }
+    if (c >= C) { v[0][c] = v[1][c] = v[2][c] = v[3][c] = 0.f; }
+  }
+  T* dst = out + ((int64_t(b) * Hp + h + off_h) * Wp + (w + off_w)) * 4;
+#pragma unroll
+  for (int px = 0; px < 4; ++px) store_pixel4<T>(dst + px * 4, v[px]);
+}
+
+// Scalar fallback: one thread per pixel, any C / Cpad / W.
 template <typename T>
 __global__ void input_xform_kernel(const float* __restrict__ in, T* __restrict__ out, int B, int C, int H, int W,
                                    int Cpad, int Hp, int Wp, int off_h, int off_w, const float* __restrict__ scale,
@@ -94,11 +149,12 @@ __global__ void input_xform_kernel(const float* __restrict__ in, T* __restrict__
 }
 
 // ---- fp32 implicit-GEMM conv ----------------------------------------------------------------
-// C[M = B*Ho*Wo][N = Cout] = A[M][K] * Wt[K][N], K ordered (ky, kx, cin).  128x64 CTA tile,
-// BK = 16, 256 threads, 8x4 register tile, double-buffered shared memory, global->register
-// prefetch of the next K slice during the FMAs.  A is gathered straight from the NHWC input in
-// float4 granules (4 consecutive channels of one tap), zero for padding taps.
-constexpr int BM = 128, BN = 64, BK = 16, SIMT_THREADS = 256;
+// C[M = B*Ho*Wo][N = Cout] = A[M][K] * Wt[K][N], K ordered (ky, kx, cin).  BM x 64 CTA tile (BM = 128
+// for convolutions, 32 for the skinny FC so that a 256-row problem still covers the chip), BK = 16,
+// 256 threads, (BM/16) x 4 register tile, double-buffered shared memory, global->register prefetch of
+// the next K slice during the FMAs.  A is gathered straight from the NHWC input in float4 granules
+// (4 consecutive channels of one tap), zero for padding taps.
+constexpr int BN = 64, BK = 16, SIMT_THREADS = 256;
 
 struct SimtConvParams {
   const float* in; const float* w;
@@ -107,42 +163,54 @@ struct SimtConvParams {
   int M, K;
 };
 
+template <int BM>
 __global__ void __launch_bounds__(SIMT_THREADS) conv_simt_f32_kernel(SimtConvParams p) {
+  constexpr int TM = BM / 16;                       // rows per thread
+  constexpr int A_VECS = BM * BK / 4;               // float4 granules of one A tile
+  constexpr int A_PER_THREAD = (A_VECS + SIMT_THREADS - 1) / SIMT_THREADS;
   __shared__ __align__(16) float As[2][BK][BM + 4];
   __shared__ __align__(16) float Bs[2][BK][BN];
   const ConvGeom& g = p.g;
   const int tid = threadIdx.x;
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
 
-  // A-load role: row ar (0..127), 8 consecutive k starting at ak
-  const int ar = tid >> 1, ak = (tid & 1) * 8;
-  const int am = m0 + ar;
-  const bool a_row_ok = am < p.M;
-  int ih0 = 0, iw0 = 0;
-  const float* a_img = p.in;
-  if (a_row_ok) {
-    int wo = am % g.Wo, t = am / g.Wo;
-    int ho = t % g.Ho, b = t / g.Ho;
-    ih0 = ho * g.stride - g.pad;
-    iw0 = wo * g.stride - g.pad;
-    a_img = p.in + int64_t(b) * g.H * g.W * g.Cin;
+  // A-load role: granule v = tid + j*256 -> row v/4, k offset (v%4)*4
+  int a_row[A_PER_THREAD], a_k[A_PER_THREAD], ih0[A_PER_THREAD], iw0[A_PER_THREAD];
+  const float* a_img[A_PER_THREAD];
+  bool a_ok[A_PER_THREAD];
+#pragma unroll
+  for (int j = 0; j < A_PER_THREAD; ++j) {
+    const int v = tid + j * SIMT_THREADS;
+    a_row[j] = v >> 2;
+    a_k[j] = (v & 3) * 4;
+    const int am = m0 + a_row[j];
+    a_ok[j] = (v < A_VECS) && (am < p.M);
+    ih0[j] = iw0[j] = 0;
+    a_img[j] = p.in;
+    if (a_ok[j]) {
+      int wo = am % g.Wo, t = am / g.Wo;
+      int ho = t % g.Ho, b = t / g.Ho;
+      ih0[j] = ho * g.stride - g.pad;
+      iw0[j] = wo * g.stride - g.pad;
+      a_img[j] = p.in + int64_t(b) * g.H * g.W * g.Cin;
+    }
   }
   // B-load role: k row bk (0..15), 4 consecutive n starting at bn
   const int bk = tid >> 4, bn = (tid & 15) * 4;
   const bool b_col_ok = (n0 + bn) < g.Cout;
 
-  float4 ra[2], rb;
+  float4 ra[A_PER_THREAD], rb;
   auto load_global = [&](int k0) {
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      int k = k0 + ak + j * 4;
+    for (int j = 0; j < A_PER_THREAD; ++j) {
+      int k = k0 + a_k[j];
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (a_row_ok && k < p.K) {
+      if (a_ok[j] && k < p.K) {
         int tap = k / g.Cin, c = k - tap * g.Cin;
         int ky = tap / g.kw, kx = tap - ky * g.kw;
-        int ih = ih0 + ky, iw = iw0 + kx;
+        int ih = ih0[j] + ky, iw = iw0[j] + kx;
         if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W)
-          v = __ldg(reinterpret_cast<const float4*>(a_img + (int64_t(ih) * g.W + iw) * g.Cin + c));
+          v = __ldg(reinterpret_cast<const float4*>(a_img[j] + (int64_t(ih) * g.W + iw) * g.Cin + c));
       }
       ra[j] = v;
     }
@@ -152,19 +220,21 @@ __global__ void __launch_bounds__(SIMT_THREADS) conv_simt_f32_kernel(SimtConvPar
   };
   auto store_smem = [&](int buf) {
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      As[buf][ak + j * 4 + 0][ar] = ra[j].x;
-      As[buf][ak + j * 4 + 1][ar] = ra[j].y;
-      As[buf][ak + j * 4 + 2][ar] = ra[j].z;
-      As[buf][ak + j * 4 + 3][ar] = ra[j].w;
+    for (int j = 0; j < A_PER_THREAD; ++j) {
+      if (tid + j * SIMT_THREADS < A_VECS) {
+        As[buf][a_k[j] + 0][a_row[j]] = ra[j].x;
+        As[buf][a_k[j] + 1][a_row[j]] = ra[j].y;
+        As[buf][a_k[j] + 2][a_row[j]] = ra[j].z;
+        As[buf][a_k[j] + 3][a_row[j]] = ra[j].w;
+      }
     }
     *reinterpret_cast<float4*>(&Bs[buf][bk][bn]) = rb;
   };
 
-  const int ty = tid >> 4, tx = tid & 15;  // 16 x 16 threads, 8 rows x 4 cols each
-  float acc[8][4];
+  const int ty = tid >> 4, tx = tid & 15;  // 16 x 16 threads, TM rows x 4 cols each
+  float acc[TM][4];
 #pragma unroll
-  for (int i = 0; i < 8; ++i)
+  for (int i = 0; i < TM; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
 
@@ -177,13 +247,24 @@ __global__ void __launch_bounds__(SIMT_THREADS) conv_simt_f32_kernel(SimtConvPar
     if (kt + 1 < KT) load_global((kt + 1) * BK);
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
-      float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8]);
-      float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8 + 4]);
+      float a[TM];
+      if constexpr (TM % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < TM; i += 4) {
+          float4 t4 = *reinterpret_cast<const float4*>(&As[buf][k][ty * TM + i]);
+          a[i] = t4.x; a[i + 1] = t4.y; a[i + 2] = t4.z; a[i + 3] = t4.w;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < TM; i += 2) {
+          float2 t2 = *reinterpret_cast<const float2*>(&As[buf][k][ty * TM + i]);
+          a[i] = t2.x; a[i + 1] = t2.y;
+        }
+      }
       float4 b = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
-      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
       const float bb[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < TM; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
     }
@@ -202,8 +283,8 @@ __global__ void __launch_bounds__(SIMT_THREADS) conv_simt_f32_kernel(SimtConvPar
     sh = __ldg(reinterpret_cast<const float4*>(e.act_shift + n));
   }
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    int m = m0 + ty * 8 + i;
+  for (int i = 0; i < TM; ++i) {
+    int m = m0 + ty * TM + i;
     if (m >= p.M) break;
     int64_t off = int64_t(m) * g.Cout + n;
     float4 v = make_float4(acc[i][0] + bias.x, acc[i][1] + bias.y, acc[i][2] + bias.z, acc[i][3] + bias.w);
@@ -355,8 +436,24 @@ __global__ void softmax_rows_kernel(const float* __restrict__ in, float* __restr
 cudaError_t launch_input_xform(const float* nchw, void* out, DType dt, int B, int C, int H, int W, int Cpad,
                                int Hp, int Wp, int off_h, int off_w, const float* scale, const float* shift,
                                int relu, cudaStream_t s) {
-  int64_t total = int64_t(B) * H * W;
-  int block = 256, grid = grid_for(total, block);
+  const int block = 256;
+  const bool vec = (W % 4 == 0) && Cpad == 4 && C <= 4 && (reinterpret_cast<uintptr_t>(nchw) % 16 == 0);
+  if (vec) {
+    const int grid = grid_for(int64_t(B) * H * (W / 4), block);
+    switch (dt) {
+      case DType::F32:
+        input_xform_vec4_kernel<float><<<grid, block, 0, s>>>(nchw, static_cast<float*>(out), B, C, H, W, Hp, Wp, off_h, off_w, scale, shift, relu);
+        break;
+      case DType::BF16:
+        input_xform_vec4_kernel<__nv_bfloat16><<<grid, block, 0, s>>>(nchw, static_cast<__nv_bfloat16*>(out), B, C, H, W, Hp, Wp, off_h, off_w, scale, shift, relu);
+        break;
+      case DType::F16:
+        input_xform_vec4_kernel<__half><<<grid, block, 0, s>>>(nchw, static_cast<__half*>(out), B, C, H, W, Hp, Wp, off_h, off_w, scale, shift, relu);
+        break;
+    }
+    return cudaGetLastError();
+  }
+  const int grid = grid_for(int64_t(B) * H * W, block);
   switch (dt) {
     case DType::F32:
       input_xform_kernel<float><<<grid, block, 0, s>>>(nchw, static_cast<float*>(out), B, C, H, W, Cpad, Hp, Wp, off_h, off_w, scale, shift, relu);
@@ -377,8 +474,15 @@ cudaError_t launch_conv_simt_f32(const float* in, const float* w, const ConvGeom
   p.in = in; p.w = w; p.e = e; p.g = g;
   p.M = g.B * g.Ho * g.Wo;
   p.K = g.kh * g.kw * g.Cin;
-  dim3 grid((p.M + BM - 1) / BM, (g.Cout + BN - 1) / BN);
-  conv_simt_f32_kernel<<<grid, SIMT_THREADS, 0, s>>>(p);
+  // a skinny problem (the FC: M = batch) takes 32-row tiles so that it still spreads over the SMs
+  const long tiles128 = long((p.M + 127) / 128) * ((g.Cout + BN - 1) / BN);
+  if (tiles128 < 2 * kSMs) {
+    dim3 grid((p.M + 31) / 32, (g.Cout + BN - 1) / BN);
+    conv_simt_f32_kernel<32><<<grid, SIMT_THREADS, 0, s>>>(p);
+  } else {
+    dim3 grid((p.M + 127) / 128, (g.Cout + BN - 1) / BN);
+    conv_simt_f32_kernel<128><<<grid, SIMT_THREADS, 0, s>>>(p);
+  }
   return cudaGetLastError();
 }
 
