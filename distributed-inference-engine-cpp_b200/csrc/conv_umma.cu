@@ -31,7 +31,10 @@
 namespace rn {
 namespace {
 
-constexpr int kThreads = 192;
+constexpr int kEpiWarps = 8;                       // two warps per TMEM lane quarter, 32 columns of a chunk each
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kBaseThreads = 64 + kEpiThreads;     // TMA warp, MMA warp, epilogue warps
+constexpr int kThreads = kBaseThreads + 128;       // + 4 operand-transform warps (layers with a prologue only)
 constexpr int kTileM = 128;
 constexpr int kChunkBytes = kTileM * 128;  // one 64-channel output chunk of a tile (16 KB)
 
@@ -40,10 +43,13 @@ struct UmmaParams {
   int bw, bh, bn, tiles_w, tiles_h;
   int n_tiles, num_stages, total_tiles, raw_bufs;
   int has_res, has_out, has_act, relu, act_relu;
+  int has_pre, pre_relu, cin;
   uint32_t a_bytes, b_bytes, rows;
   const float* bias;
   const float* act_scale;
   const float* act_shift;
+  const float* pre_scale;
+  const float* pre_shift;
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------------
@@ -216,7 +222,12 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
-template <typename T, int BLOCK_N, int KB>
+// EPI >= 0: epilogue flags fixed at compile time (bit 0 ReLU, 1 residual, 2 raw output, 3 activated
+// output, 4 ReLU on the activated output) so that unused math is not even issued -- the epilogue warps
+// are issue-bound on the memory-bound layers.  EPI < 0: flags read from the parameters (any combination).
+enum : int { EPI_RELU = 1, EPI_RES = 2, EPI_OUT = 4, EPI_ACT = 8, EPI_ACT_RELU = 16 };
+
+template <typename T, int BLOCK_N, int KB, int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
@@ -238,16 +249,24 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   float* s_bias = reinterpret_cast<float*>(tail);
   float* s_scale = s_bias + BLOCK_N;
   float* s_shift = s_scale + BLOCK_N;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_shift + BLOCK_N);
-  uint64_t* full_bar = bars;                  // [S]  TMA -> MMA
+  float* s_pre_scale = s_shift + BLOCK_N;      // [cin] each, only when has_pre
+  float* s_pre_shift = s_pre_scale + (p.has_pre ? p.cin : 0);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_pre_shift + (p.has_pre ? p.cin : 0));
+  uint64_t* full_bar = bars;                  // [S]  TMA -> MMA (or -> transform warps when has_pre)
   uint64_t* empty_bar = bars + S;             // [S]  MMA -> TMA
   uint64_t* tmem_full = bars + 2 * S;         // [2]  MMA -> epilogue
   uint64_t* tmem_empty = tmem_full + 2;       // [2]  epilogue -> MMA (128 arrivals)
   uint64_t* res_full = tmem_empty + 2;        // [2]  TMA -> epilogue
   uint64_t* res_empty = res_full + 2;         // [2]  epilogue -> TMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_empty + 2);
+  uint64_t* xf_bar = res_empty + 2;           // [S]  transform warps -> MMA (128 arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xf_bar + S);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool f_relu = EPI >= 0 ? bool(EPI & EPI_RELU) : bool(p.relu);
+  const bool f_res = EPI >= 0 ? bool(EPI & EPI_RES) : bool(p.has_res);
+  const bool f_out = EPI >= 0 ? bool(EPI & EPI_OUT) : bool(p.has_out);
+  const bool f_act = EPI >= 0 ? bool(EPI & EPI_ACT) : bool(p.has_act);
+  const bool f_act_relu = EPI >= 0 ? bool(EPI & EPI_ACT_RELU) : bool(p.act_relu);
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
@@ -258,16 +277,22 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int i = 0; i < S; ++i) {
       mbar_init(smem_u32(&full_bar[i]), 1);
       mbar_init(smem_u32(&empty_bar[i]), 1);
+      mbar_init(smem_u32(&xf_bar[i]), 128);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&tmem_full[i]), 1);
-      mbar_init(smem_u32(&tmem_empty[i]), 128);
+      mbar_init(smem_u32(&tmem_empty[i]), kEpiThreads);
       mbar_init(smem_u32(&res_full[i]), 1);
       mbar_init(smem_u32(&res_empty[i]), 1);
     }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * BLOCK_N);
+  if (p.has_pre)
+    for (int k = threadIdx.x; k < p.cin; k += blockDim.x) {
+      s_pre_scale[k] = __ldg(p.pre_scale + k);
+      s_pre_shift[k] = __ldg(p.pre_shift + k);
+    }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -321,7 +346,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
       for (int it = 0; it < p.num_k_iters; ++it) {
-        mbar_wait(smem_u32(&full_bar[stage]), phase);
+        mbar_wait(smem_u32(p.has_pre ? &xf_bar[stage] : &full_bar[stage]), phase);
         tc_fence_after();
         if (elect_one()) {
           const uint32_t a_addr = smem_u32(pipe + stage * STAGE_BYTES);
@@ -339,12 +364,54 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (++stage == S) { stage = 0; phase ^= 1; }
       }
     }
+  } else if (warp >= 2 + kEpiWarps) {
+    // ===== operand transform (has_pre only): A' = relu?(pre_scale[c] * A + pre_shift[c]) in place =====
+    // (these four warps are only launched for layers with a prologue)
+    // thread = one 16-byte channel chunk (8 channels) of every 16th row, so its 8 scale/shift pairs stay in
+    // registers for the whole K block; a warp touches 4 complete 128-byte rows per access (conflict-free).
+    // Chunk j of row r sits at 16-byte slot (j ^ (r & 7)) of the row (SWIZZLE_128B).
+    const int t = threadIdx.x - kBaseThreads;
+    const int j = t & 7;
+    const int r0 = t >> 3;                   // rows r0, r0+16, ..., r0+112
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      for (int it = 0; it < p.num_k_iters; ++it) {
+        const int cb = it % p.cblks;
+        const float4 s0 = *reinterpret_cast<const float4*>(s_pre_scale + cb * 64 + j * 8);
+        const float4 s1 = *reinterpret_cast<const float4*>(s_pre_scale + cb * 64 + j * 8 + 4);
+        const float4 t0 = *reinterpret_cast<const float4*>(s_pre_shift + cb * 64 + j * 8);
+        const float4 t1 = *reinterpret_cast<const float4*>(s_pre_shift + cb * 64 + j * 8 + 4);
+        mbar_wait(smem_u32(&full_bar[stage]), phase);
+        uint8_t* a_tile = pipe + stage * STAGE_BYTES;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = r0 + i * 16;
+          uint4* ptr = reinterpret_cast<uint4*>(a_tile + r * 128 + ((j ^ (r & 7)) << 4));
+          const uint4 q = *ptr;
+          float2 x0 = unpack2<T>(q.x), x1 = unpack2<T>(q.y), x2 = unpack2<T>(q.z), x3 = unpack2<T>(q.w);
+          x0.x = fmaf(s0.x, x0.x, t0.x); x0.y = fmaf(s0.y, x0.y, t0.y);
+          x1.x = fmaf(s0.z, x1.x, t0.z); x1.y = fmaf(s0.w, x1.y, t0.w);
+          x2.x = fmaf(s1.x, x2.x, t1.x); x2.y = fmaf(s1.y, x2.y, t1.y);
+          x3.x = fmaf(s1.z, x3.x, t1.z); x3.y = fmaf(s1.w, x3.y, t1.w);
+          if (p.pre_relu) {
+            x0.x = fmaxf(x0.x, 0.f); x0.y = fmaxf(x0.y, 0.f); x1.x = fmaxf(x1.x, 0.f); x1.y = fmaxf(x1.y, 0.f);
+            x2.x = fmaxf(x2.x, 0.f); x2.y = fmaxf(x2.y, 0.f); x3.x = fmaxf(x3.x, 0.f); x3.y = fmaxf(x3.y, 0.f);
+          }
+          *ptr = make_uint4(pack2<T>(x0.x, x0.y), pack2<T>(x1.x, x1.y), pack2<T>(x2.x, x2.y), pack2<T>(x3.x, x3.y));
+        }
+        fence_proxy_async_smem();            // generic-proxy writes -> visible to the tensor core's reads
+        mbar_arrive(smem_u32(&xf_bar[stage]));
+        if (++stage == S) { stage = 0; phase ^= 1; }
+      }
+    }
   } else {
-    // ===== epilogue: 4 warps, thread = one output pixel (TMEM lane) =====
+    // ===== epilogue: 8 warps; thread = one output pixel (TMEM lane) x 32 of a chunk's 64 channels =====
     const int q = warp & 3;                 // TMEM lane quarter this warp may access
+    const int g = (warp - 2) >> 2;          // which half of every 64-channel chunk (16-byte slots 4g..4g+3)
     const int row = q * 32 + lane;
     const int sw = row & 7;
-    const int et = threadIdx.x - 64;        // 0..127
+    const int et = threadIdx.x - 64;        // 0..255
     const bool store_thread = (warp == 2 && lane == 0);
     int cur_ntile = -1;
     int i = 0;
@@ -354,33 +421,29 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t par = (i >> 1) & 1;
       if (tc.n_tile != cur_ntile) {         // per-channel parameters of this N tile
         cur_ntile = tc.n_tile;
-        for (int k = et; k < BLOCK_N; k += 128) {
+        for (int k = et; k < BLOCK_N; k += kEpiThreads) {
           s_bias[k] = __ldg(p.bias + tc.col0 + k);
-          s_scale[k] = p.has_act ? __ldg(p.act_scale + tc.col0 + k) : 1.f;
-          s_shift[k] = p.has_act ? __ldg(p.act_shift + tc.col0 + k) : 0.f;
+          if (f_act) {
+            s_scale[k] = __ldg(p.act_scale + tc.col0 + k);
+            s_shift[k] = __ldg(p.act_shift + tc.col0 + k);
+          }
         }
       }
       if (store_thread && i > 0) {
         tma_store_wait_read();              // previous tile's stores have read their staging buffers
-        if (p.has_res) mbar_arrive(smem_u32(&res_empty[(p.raw_bufs == 2) ? ((i - 1) & 1) : 0]));
+        if (f_res) mbar_arrive(smem_u32(&res_empty[(p.raw_bufs == 2) ? ((i - 1) & 1) : 0]));
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       mbar_wait(smem_u32(&tmem_full[buf]), par);
       tc_fence_after();
       const int rb = (p.raw_bufs == 2) ? (i & 1) : 0;
-      if (p.has_res) mbar_wait(smem_u32(&res_full[rb]), (p.raw_bufs == 2) ? par : uint32_t(i & 1));
+      if (f_res) mbar_wait(smem_u32(&res_full[rb]), (p.raw_bufs == 2) ? par : uint32_t(i & 1));
       uint8_t* raw_tile = rawbuf + rb * RAW_BYTES;
 #pragma unroll 1
       for (int c = 0; c < kChunks; ++c) {
-        uint32_t acc[64];
-        {
-          uint32_t (&lo)[32] = *reinterpret_cast<uint32_t (*)[32]>(&acc[0]);
-          uint32_t (&hi)[32] = *reinterpret_cast<uint32_t (*)[32]>(&acc[32]);
-          const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(buf * BLOCK_N + c * 64);
-          tmem_ld_32x32b_x32(taddr, lo);
-          tmem_ld_32x32b_x32(taddr + 32, hi);
-          tmem_ld_wait();
-        }
+        uint32_t acc[32];
+        tmem_ld_32x32b_x32(tmem_base + (uint32_t(q * 32) << 16) + uint32_t(buf * BLOCK_N + c * 64 + g * 32), acc);
+        tmem_ld_wait();
         if (c == kChunks - 1) {             // accumulator fully read: hand it back to the MMA warp
           tc_fence_before();
           mbar_arrive(smem_u32(&tmem_empty[buf]));
@@ -390,37 +453,49 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint4* raw_row = reinterpret_cast<uint4*>(raw_stage + row * 128);
         uint4* act_row = reinterpret_cast<uint4*>(act_stage + row * 128);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {         // 8 channels (16 bytes) at a time
+        for (int jj = 0; jj < 4; ++jj) {      // 8 channels (16 bytes) at a time
+          const int j = g * 4 + jj;
+          const int col = c * 64 + j * 8;
+          const float4 b0 = *reinterpret_cast<const float4*>(s_bias + col);
+          const float4 b1 = *reinterpret_cast<const float4*>(s_bias + col + 4);
           float v[8];
+          v[0] = __uint_as_float(acc[jj * 8 + 0]) + b0.x; v[1] = __uint_as_float(acc[jj * 8 + 1]) + b0.y;
+          v[2] = __uint_as_float(acc[jj * 8 + 2]) + b0.z; v[3] = __uint_as_float(acc[jj * 8 + 3]) + b0.w;
+          v[4] = __uint_as_float(acc[jj * 8 + 4]) + b1.x; v[5] = __uint_as_float(acc[jj * 8 + 5]) + b1.y;
+          v[6] = __uint_as_float(acc[jj * 8 + 6]) + b1.z; v[7] = __uint_as_float(acc[jj * 8 + 7]) + b1.w;
+          if (f_relu) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            v[k] = __uint_as_float(acc[j * 8 + k]) + s_bias[c * 64 + j * 8 + k];
-            if (p.relu) v[k] = fmaxf(v[k], 0.f);
+            for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
           }
           const int slot = j ^ sw;            // SWIZZLE_128B: 16-byte chunk index XOR (row mod 8)
-          if (p.has_res) {
+          if (f_res) {
             const uint4 r = raw_row[slot];
             const float2 r0 = unpack2<T>(r.x), r1 = unpack2<T>(r.y), r2 = unpack2<T>(r.z), r3 = unpack2<T>(r.w);
             v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
             v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
           }
-          if (p.has_out)
+          if (f_out)
             raw_row[slot] = make_uint4(pack2<T>(v[0], v[1]), pack2<T>(v[2], v[3]), pack2<T>(v[4], v[5]), pack2<T>(v[6], v[7]));
-          if (p.has_act) {
+          if (f_act) {
+            const float4 s0 = *reinterpret_cast<const float4*>(s_scale + col);
+            const float4 s1 = *reinterpret_cast<const float4*>(s_scale + col + 4);
+            const float4 t0 = *reinterpret_cast<const float4*>(s_shift + col);
+            const float4 t1 = *reinterpret_cast<const float4*>(s_shift + col + 4);
             float a[8];
+            a[0] = fmaf(s0.x, v[0], t0.x); a[1] = fmaf(s0.y, v[1], t0.y); a[2] = fmaf(s0.z, v[2], t0.z); a[3] = fmaf(s0.w, v[3], t0.w);
+            a[4] = fmaf(s1.x, v[4], t1.x); a[5] = fmaf(s1.y, v[5], t1.y); a[6] = fmaf(s1.z, v[6], t1.z); a[7] = fmaf(s1.w, v[7], t1.w);
+            if (f_act_relu) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              a[k] = fmaf(s_scale[c * 64 + j * 8 + k], v[k], s_shift[c * 64 + j * 8 + k]);
-              if (p.act_relu) a[k] = fmaxf(a[k], 0.f);
+              for (int k = 0; k < 8; ++k) a[k] = fmaxf(a[k], 0.f);
             }
             act_row[slot] = make_uint4(pack2<T>(a[0], a[1]), pack2<T>(a[2], a[3]), pack2<T>(a[4], a[5]), pack2<T>(a[6], a[7]));
           }
         }
         fence_proxy_async_smem();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         if (store_thread) {
-          if (p.has_out) tma_store_4d(&tmOut, smem_u32(raw_stage), tc.col0 + c * 64, tc.w0, tc.h0, tc.n0);
-          if (p.has_act) tma_store_4d(&tmAct, smem_u32(act_stage), tc.col0 + c * 64, tc.w0, tc.h0, tc.n0);
+          if (f_out) tma_store_4d(&tmOut, smem_u32(raw_stage), tc.col0 + c * 64, tc.w0, tc.h0, tc.n0);
+          if (f_act) tma_store_4d(&tmAct, smem_u32(act_stage), tc.col0 + c * 64, tc.w0, tc.h0, tc.n0);
           tma_store_commit();
         }
       }
@@ -594,7 +669,7 @@ static void plan_geometry(UmmaConvPlan& pl) {
   auto fixed_bytes = [&](int bn, int nb) {
     const uint32_t raw_bytes = uint32_t(bn / 64) * kChunkBytes;
     return 1024u + ((p.has_out || p.has_res) ? uint32_t(nb) * raw_bytes : 0u) + (p.has_act ? raw_bytes : 0u) +
-           3u * uint32_t(bn) * 4 + 8u * (2 * 8 + 8) + 64;
+           3u * uint32_t(bn) * 4 + (p.has_pre ? 8u * uint32_t(g.Cin) : 0u) + 8u * (3 * 8 + 8) + 64;
   };
   auto stage_bytes_of = [&](int bn) { return uint32_t(kTileM * pl.kb + bn * pl.kb); };
   int best_bn = 64;
@@ -630,9 +705,9 @@ static void plan_geometry(UmmaConvPlan& pl) {
   pl.grid = std::min(p.total_tiles, sms);
 }
 
-template <typename T, int BLOCK_N, int KB>
+template <typename T, int BLOCK_N, int KB, int EPI>
 static cudaError_t launch_inst(const UmmaConvPlan* pl, cudaStream_t s) {
-  auto kern = conv_umma_kernel<T, BLOCK_N, KB>;
+  auto kern = conv_umma_kernel<T, BLOCK_N, KB, EPI>;
   static thread_local int configured_device = -1;  // per (instantiation, thread)
   int dev = 0;
   cudaGetDevice(&dev);
@@ -641,16 +716,32 @@ static cudaError_t launch_inst(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  kern<<<pl->grid, kThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->p);
+  // the four operand-transform warps exist only for layers that need them
+  kern<<<pl->grid, pl->p.has_pre ? kThreads : kBaseThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->p);
   return cudaGetLastError();
+}
+
+template <typename T, int BLOCK_N, int KB>
+static cudaError_t launch_epi(const UmmaConvPlan* pl, cudaStream_t s) {
+  const UmmaParams& p = pl->p;
+  const int flags = (p.relu ? EPI_RELU : 0) | (p.has_res ? EPI_RES : 0) | (p.has_out ? EPI_OUT : 0) |
+                    (p.has_act ? EPI_ACT : 0) | ((p.has_act && p.act_relu) ? EPI_ACT_RELU : 0);
+  switch (flags) {   // the combinations a ResNet produces get their own code; anything else runs the generic one
+    case EPI_OUT | EPI_RELU: return launch_inst<T, BLOCK_N, KB, EPI_OUT | EPI_RELU>(pl, s);
+    case EPI_OUT: return launch_inst<T, BLOCK_N, KB, EPI_OUT>(pl, s);
+    case EPI_OUT | EPI_RES: return launch_inst<T, BLOCK_N, KB, EPI_OUT | EPI_RES>(pl, s);
+    case EPI_OUT | EPI_RES | EPI_ACT | EPI_ACT_RELU: return launch_inst<T, BLOCK_N, KB, EPI_OUT | EPI_RES | EPI_ACT | EPI_ACT_RELU>(pl, s);
+    case EPI_RES | EPI_ACT | EPI_ACT_RELU: return launch_inst<T, BLOCK_N, KB, EPI_RES | EPI_ACT | EPI_ACT_RELU>(pl, s);
+    default: return launch_inst<T, BLOCK_N, KB, -1>(pl, s);
+  }
 }
 
 cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
   const bool bf = pl->dt == DType::BF16;
-  if (pl->kb == 64) return bf ? launch_inst<__nv_bfloat16, 64, 64>(pl, s) : launch_inst<__half, 64, 64>(pl, s);
-  if (pl->block_n == 64) return bf ? launch_inst<__nv_bfloat16, 64, 128>(pl, s) : launch_inst<__half, 64, 128>(pl, s);
-  if (pl->block_n == 128) return bf ? launch_inst<__nv_bfloat16, 128, 128>(pl, s) : launch_inst<__half, 128, 128>(pl, s);
-  return bf ? launch_inst<__nv_bfloat16, 256, 128>(pl, s) : launch_inst<__half, 256, 128>(pl, s);
+  if (pl->kb == 64) return bf ? launch_epi<__nv_bfloat16, 64, 64>(pl, s) : launch_epi<__half, 64, 64>(pl, s);
+  if (pl->block_n == 64) return bf ? launch_epi<__nv_bfloat16, 64, 128>(pl, s) : launch_epi<__half, 64, 128>(pl, s);
+  if (pl->block_n == 128) return bf ? launch_epi<__nv_bfloat16, 128, 128>(pl, s) : launch_epi<__half, 128, 128>(pl, s);
+  return bf ? launch_epi<__nv_bfloat16, 256, 128>(pl, s) : launch_epi<__half, 256, 128>(pl, s);
 }
 
 UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in, const void* w_packed,
@@ -669,6 +760,9 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   p.has_res = e.residual != nullptr; p.has_out = e.out != nullptr; p.has_act = e.out_act != nullptr;
   p.relu = e.relu; p.act_relu = e.act_relu;
   p.bias = e.bias; p.act_scale = e.act_scale; p.act_shift = e.act_shift;
+  p.has_pre = e.pre_scale != nullptr; p.pre_relu = e.pre_relu; p.cin = g.Cin;
+  p.pre_scale = e.pre_scale; p.pre_shift = e.pre_shift;
+  if (p.has_pre && (stem_mode || g.kh != 1 || g.kw != 1 || g.pad != 0)) { delete pl; return failmsg("operand prologue needs a 1x1, pad-0 conv"); }
   if (!p.has_out && !p.has_act) { delete pl; return failmsg("conv with no output"); }
   plan_geometry(*pl);
   const int bw = p.bw, bh = p.bh, bn = p.bn;

@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -36,6 +37,14 @@ std::string fmt(const char* f, ...) {
   return buf;
 }
 
+// B200RN_PROLOGUE=1 applies "residual sum -> BN -> ReLU" inside the reading 1x1 convs' operand staging instead of
+// writing an activated copy from the producer.  Measured on B200 it is a wash at batch 256 and a
+// small loss at batch 32, so it is off unless asked for.
+bool prologue_enabled() {
+  const char* v = std::getenv("B200RN_PROLOGUE");
+  return v && v[0] == '1';
+}
+
 struct CudaFail { std::string msg; };
 #define CK(expr)                                                                                       \
   do {                                                                                                 \
@@ -52,9 +61,13 @@ struct DevLayer {
   float* bias = nullptr;
   float* act_scale = nullptr;
   float* act_shift = nullptr;
+  float* pre_scale = nullptr;
+  float* pre_shift = nullptr;
   void* w = nullptr;
   bool umma = false;
   int stem = 0;
+  float* splitk = nullptr;              // Gemm only: split-K partial sums + tile counters
+  size_t splitk_bytes = 0;
   std::map<int, UmmaConvPlan*> plans;   // per batch size
   double weight_bytes = 0;
 };
@@ -99,7 +112,8 @@ struct b200rn {
   ~b200rn() {
     cudaSetDevice(device);
     for (auto& L : dl) {
-      cudaFree(L.bias); cudaFree(L.act_scale); cudaFree(L.act_shift); cudaFree(L.w);
+      cudaFree(L.bias); cudaFree(L.act_scale); cudaFree(L.act_shift); cudaFree(L.w); cudaFree(L.splitk);
+      cudaFree(L.pre_scale); cudaFree(L.pre_shift);
       for (auto& kv : L.plans) umma_conv_plan_destroy(kv.second);
     }
     cudaFree(arena);
@@ -166,7 +180,7 @@ struct b200rn {
 
   void build(const std::string& path) {
     OnnxModel model = load_onnx(path);
-    plan = build_plan(model, dt == DType::F32 ? 4 : 8);
+    plan = build_plan(model, dt == DType::F32 ? 4 : 8, prologue_enabled());
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&s_h2d, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&s_compute, cudaStreamNonBlocking));
@@ -178,6 +192,10 @@ struct b200rn {
       D.bias = upload(L.bias);
       D.act_scale = upload(L.act_scale);
       D.act_shift = upload(L.act_shift);
+      if (L.kind == LayerKind::Conv) {
+        D.pre_scale = upload(L.pre_scale);
+        D.pre_shift = upload(L.pre_shift);
+      }
       if (L.kind == LayerKind::Conv || L.kind == LayerKind::Gemm) {
         const bool fast_conv = L.kind == LayerKind::Conv && dt != DType::F32;
         if (fast_conv) {
@@ -203,6 +221,11 @@ struct b200rn {
             for (int k = 0; k < K; ++k) wt[size_t(k) * L.Cout + o] = L.weight[size_t(o) * K + k];
           D.w = upload(wt);
           D.weight_bytes = double(wt.size()) * 4;
+          if (L.kind == LayerKind::Gemm) {
+            D.splitk_bytes = simt_splitk_scratch_bytes(max_batch, L.Cout);
+            CK(cudaMalloc(&D.splitk, D.splitk_bytes));
+            CK(cudaMemset(D.splitk, 0, D.splitk_bytes));
+          }
         }
       }
     }
@@ -254,6 +277,7 @@ struct b200rn {
       case LayerKind::Conv: {
         ConvGeom g = geom(L, B);
         e.residual = tptr(L.in2);
+        e.pre_scale = D.pre_scale; e.pre_shift = D.pre_shift; e.pre_relu = L.pre_relu;
         if (D.umma) {
           UmmaConvPlan*& up = D.plans[B];
           if (!up) {
@@ -272,7 +296,8 @@ struct b200rn {
         ConvGeom g{B, 1, 1, L.Cin, 1, 1, L.Cout, 1, 1, 1, 0};
         Epilogue ge;
         ge.bias = D.bias; ge.out = out_ptr(L.out);
-        CK(launch_conv_simt_f32(static_cast<const float*>(tptr(L.in)), static_cast<const float*>(D.w), g, ge, s));
+        CK(launch_conv_simt_f32(static_cast<const float*>(tptr(L.in)), static_cast<const float*>(D.w), g, ge, s,
+                                D.splitk, D.splitk_bytes));
         break;
       }
       case LayerKind::MaxPool: {
@@ -521,7 +546,7 @@ int64_t b200rn_describe_plan(const char* onnx_path, int mode, char* buf, size_t 
   std::string text;
   int rc = guarded(nullptr, [&] {
     OnnxModel m = load_onnx(onnx_path);
-    Plan p = build_plan(m, mode == B200RN_MODE_EXACT ? 4 : 8);
+    Plan p = build_plan(m, mode == B200RN_MODE_EXACT ? 4 : 8, prologue_enabled());
     text = p.describe();
   });
   if (rc != B200RN_OK) return -1;
@@ -614,8 +639,13 @@ int b200rn_time_forward(b200rn_t* h, const float* const* d_inputs, int n_inputs,
 
 int b200rn_conv2d(int dtype, const void* d_in, int B, int H, int W, int Cin, const float* w, const float* bias,
                   int Cout, int kh, int kw, int stride, int pad, int relu, const void* d_residual, void* d_out,
-                  void* d_out_act, const float* act_scale, const float* act_shift, int act_relu) {
+                  void* d_out_act, const float* act_scale, const float* act_shift, int act_relu,
+                  const float* pre_scale, const float* pre_shift, int pre_relu) {
   if (!d_in || !w || (!d_out && !d_out_act) || dtype < 0 || dtype > 2) { g_error = "b200rn_conv2d: bad argument"; return B200RN_ERR_ARG; }
+  if ((pre_scale != nullptr) != (pre_shift != nullptr) || (pre_scale && (kh != 1 || kw != 1 || pad != 0))) {
+    g_error = "b200rn_conv2d: the operand prologue needs both arrays and a 1x1, pad-0 conv";
+    return B200RN_ERR_ARG;
+  }
   return guarded(nullptr, [&] {
     DType dt = DType(dtype);
     const int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
@@ -625,9 +655,16 @@ int b200rn_conv2d(int dtype, const void* d_in, int B, int H, int W, int Cin, con
     std::vector<float> hs(act_scale ? act_scale : ones.data(), (act_scale ? act_scale : ones.data()) + Cout);
     std::vector<float> ht(act_shift ? act_shift : zeros.data(), (act_shift ? act_shift : zeros.data()) + Cout);
     float* db = upload(hb); float* ds = upload(hs); float* dsh = upload(ht);
+    float* dps = nullptr; float* dpt = nullptr;
+    if (pre_scale) {
+      dps = upload(std::vector<float>(pre_scale, pre_scale + Cin));
+      dpt = upload(std::vector<float>(pre_shift, pre_shift + Cin));
+    }
+    struct Cleanup { float* a; float* b; ~Cleanup() { cudaFree(a); cudaFree(b); } } cleanup{dps, dpt};
     Epilogue e;
     e.bias = db; e.act_scale = ds; e.act_shift = dsh; e.relu = relu; e.act_relu = act_relu;
     e.residual = d_residual; e.out = d_out; e.out_act = d_out_act;
+    e.pre_scale = dps; e.pre_shift = dpt; e.pre_relu = pre_relu;
     void* dw = nullptr;
     if (dt == DType::F32) {
       const int K = kh * kw * Cin;

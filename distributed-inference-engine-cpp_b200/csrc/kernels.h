@@ -16,7 +16,12 @@ inline size_t dtype_size(DType t) { return t == DType::F32 ? 4 : 2; }
 //   v = acc + bias[c];  if (relu) v = max(v, 0);  if (residual) v += residual[m][c];
 //   if (out)     out[m][c]     = v;
 //   if (out_act) out_act[m][c] = act_relu ? max(act_scale[c]*v + act_shift[c], 0) : act_scale[c]*v + act_shift[c];
+// Optional prologue (1x1, pad-0 convs only): the input is read as
+//   x' = pre_relu ? max(pre_scale[c]*x + pre_shift[c], 0) : pre_scale[c]*x + pre_shift[c]
 struct Epilogue {
+  const float* pre_scale = nullptr;
+  const float* pre_shift = nullptr;
+  int pre_relu = 0;
   const float* bias = nullptr;
   const void* residual = nullptr;
   void* out = nullptr;
@@ -42,7 +47,11 @@ cudaError_t launch_input_xform(const float* nchw, void* out, DType dt, int B, in
 
 // fp32 implicit-GEMM convolution on CUDA cores (exact mode, and the tiny FC in every mode).
 // w: [K = kh*kw*Cin][Cout] fp32.
-cudaError_t launch_conv_simt_f32(const float* in, const float* w, const ConvGeom& g, const Epilogue& e, cudaStream_t s);
+// splitk_scratch (optional, zero-initialised device memory of simt_splitk_scratch_bytes()) lets a skinny
+// problem split K across CTAs with a deterministic in-kernel reduction.
+cudaError_t launch_conv_simt_f32(const float* in, const float* w, const ConvGeom& g, const Epilogue& e, cudaStream_t s,
+                                 float* splitk_scratch = nullptr, size_t splitk_scratch_bytes = 0);
+size_t simt_splitk_scratch_bytes(int max_rows, int Cout);
 
 // max-pool k x k / stride / pad (padding excluded from the max), NHWC, with optional second output.
 cudaError_t launch_maxpool(const void* in, DType dt, int B, int H, int W, int C, int Ho, int Wo, int k, int stride,

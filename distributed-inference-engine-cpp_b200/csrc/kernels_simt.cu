@@ -5,6 +5,8 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
+#include <algorithm>
+
 #include "kernels.h"
 
 namespace rn {
@@ -161,6 +163,12 @@ struct SimtConvParams {
   Epilogue e;
   ConvGeom g;
   int M, K;
+  // split-K (skinny problems only): blockIdx.z walks K slices of k_per_slice; partial sums go to
+  // `partial` [slices][M][Cout]; the last CTA to finish a tile (ticket from `counters`) adds the
+  // slices in index order -- a fixed order, so the result is bit-reproducible -- and runs the epilogue.
+  int slices, k_per_slice;
+  float* partial;
+  unsigned int* counters;
 };
 
 template <int BM>
@@ -209,8 +217,15 @@ __global__ void __launch_bounds__(SIMT_THREADS) conv_simt_f32_kernel(SimtConvPar
         int tap = k / g.Cin, c = k - tap * g.Cin;
         int ky = tap / g.kw, kx = tap - ky * g.kw;
         int ih = ih0[j] + ky, iw = iw0[j] + kx;
-        if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W)
+        if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W) {
           v = __ldg(reinterpret_cast<const float4*>(a_img[j] + (int64_t(ih) * g.W + iw) * g.Cin + c));
+          if (p.e.pre_scale) {   // BN -> ReLU of the producer side, applied on the way in
+            const float4 ps = __ldg(reinterpret_cast<const float4*>(p.e.pre_scale + c));
+            const float4 pt = __ldg(reinterpret_cast<const float4*>(p.e.pre_shift + c));
+            v.x = fmaf(ps.x, v.x, pt.x); v.y = fmaf(ps.y, v.y, pt.y); v.z = fmaf(ps.z, v.z, pt.z); v.w = fmaf(ps.w, v.w, pt.w);
+            if (p.e.pre_relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+          }
+        }
       }
       ra[j] = v;
     }
@@ -238,13 +253,15 @@ __global__ void __launch_bounds__(SIMT_THREADS) conv_simt_f32_kernel(SimtConvPar
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
 
-  const int KT = (p.K + BK - 1) / BK;
-  load_global(0);
+  const int k_begin = (p.slices > 1) ? blockIdx.z * p.k_per_slice : 0;
+  const int k_end = (p.slices > 1) ? min(p.K, k_begin + p.k_per_slice) : p.K;
+  const int KT = (k_end - k_begin + BK - 1) / BK;
+  load_global(k_begin);
   store_smem(0);
   __syncthreads();
   for (int kt = 0; kt < KT; ++kt) {
     const int buf = kt & 1;
-    if (kt + 1 < KT) load_global((kt + 1) * BK);
+    if (kt + 1 < KT) load_global(k_begin + (kt + 1) * BK);
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
       float a[TM];
@@ -272,8 +289,41 @@ __global__ void __launch_bounds__(SIMT_THREADS) conv_simt_f32_kernel(SimtConvPar
     __syncthreads();
   }
 
-  // fused epilogue
   const int n = n0 + tx * 4;
+  if (p.slices > 1) {
+    // publish this slice, then let the last arrival of the tile reduce all slices in order
+    __shared__ unsigned int s_ticket;
+    if (n < g.Cout) {
+#pragma unroll
+      for (int i = 0; i < TM; ++i) {
+        int m = m0 + ty * TM + i;
+        if (m < p.M)
+          *reinterpret_cast<float4*>(p.partial + (int64_t(blockIdx.z) * p.M + m) * g.Cout + n) =
+              make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+      }
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_ticket = atomicAdd(p.counters + blockIdx.y * gridDim.x + blockIdx.x, 1u);
+    __syncthreads();
+    if (s_ticket != unsigned(p.slices - 1)) return;
+    __threadfence();
+    if (tid == 0) p.counters[blockIdx.y * gridDim.x + blockIdx.x] = 0;   // ready for the next launch
+    if (n < g.Cout) {
+#pragma unroll
+      for (int i = 0; i < TM; ++i) {
+        int m = m0 + ty * TM + i;
+        if (m >= p.M) break;
+        float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int z = 0; z < p.slices; ++z) {
+          float4 v = __ldcg(reinterpret_cast<const float4*>(p.partial + (int64_t(z) * p.M + m) * g.Cout + n));
+          sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+        }
+        acc[i][0] = sum.x; acc[i][1] = sum.y; acc[i][2] = sum.z; acc[i][3] = sum.w;
+      }
+    }
+  }
+  // fused epilogue
   if (n >= g.Cout) return;
   const Epilogue& e = p.e;
   const float4 bias = __ldg(reinterpret_cast<const float4*>(e.bias + n));
@@ -468,22 +518,45 @@ cudaError_t launch_input_xform(const float* nchw, void* out, DType dt, int B, in
   return cudaGetLastError();
 }
 
-cudaError_t launch_conv_simt_f32(const float* in, const float* w, const ConvGeom& g, const Epilogue& e, cudaStream_t s) {
+cudaError_t launch_conv_simt_f32(const float* in, const float* w, const ConvGeom& g, const Epilogue& e, cudaStream_t s,
+                                 float* splitk_scratch, size_t splitk_scratch_bytes) {
   if (g.Cin % 4 || g.Cout % 4) return cudaErrorInvalidValue;
   SimtConvParams p;
   p.in = in; p.w = w; p.e = e; p.g = g;
   p.M = g.B * g.Ho * g.Wo;
   p.K = g.kh * g.kw * g.Cin;
-  // a skinny problem (the FC: M = batch) takes 32-row tiles so that it still spreads over the SMs
+  p.slices = 1; p.k_per_slice = p.K; p.partial = nullptr; p.counters = nullptr;
+  // a skinny problem (the FC: M = batch) takes 32-row tiles and, given scratch, split-K, so that it
+  // still spreads over the SMs
   const long tiles128 = long((p.M + 127) / 128) * ((g.Cout + BN - 1) / BN);
   if (tiles128 < 2 * kSMs) {
-    dim3 grid((p.M + 31) / 32, (g.Cout + BN - 1) / BN);
+    dim3 grid((p.M + 31) / 32, (g.Cout + BN - 1) / BN, 1);
+    const long tiles = long(grid.x) * grid.y;
+    if (splitk_scratch && tiles < 4 * kSMs) {
+      int slices = int(std::min<long>(16, (4 * kSMs + tiles - 1) / tiles));
+      int per = ((p.K + slices - 1) / slices + BK - 1) / BK * BK;
+      slices = (p.K + per - 1) / per;
+      const size_t counter_bytes = (size_t(tiles) * 4 + 255) / 256 * 256;
+      const size_t need = counter_bytes + size_t(slices) * p.M * g.Cout * 4;
+      if (slices > 1 && need <= splitk_scratch_bytes) {
+        p.slices = slices; p.k_per_slice = per;
+        p.counters = reinterpret_cast<unsigned int*>(splitk_scratch);   // zeroed at allocation, self-resetting
+        p.partial = reinterpret_cast<float*>(reinterpret_cast<char*>(splitk_scratch) + counter_bytes);
+        grid.z = unsigned(slices);
+      }
+    }
     conv_simt_f32_kernel<32><<<grid, SIMT_THREADS, 0, s>>>(p);
   } else {
     dim3 grid((p.M + 127) / 128, (g.Cout + BN - 1) / BN);
     conv_simt_f32_kernel<128><<<grid, SIMT_THREADS, 0, s>>>(p);
   }
   return cudaGetLastError();
+}
+
+size_t simt_splitk_scratch_bytes(int max_rows, int Cout) {
+  // 16 slices of partial sums + one ticket counter per 32x64 tile
+  const size_t tiles = size_t((max_rows + 31) / 32) * ((Cout + BN - 1) / BN);
+  return (tiles * 4 + 255) / 256 * 256 + size_t(16) * max_rows * Cout * 4;
 }
 
 cudaError_t launch_maxpool(const void* in, DType dt, int B, int H, int W, int C, int Ho, int Wo, int k, int stride,

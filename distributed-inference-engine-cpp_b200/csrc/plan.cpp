@@ -30,9 +30,18 @@ namespace {
 
 int round_up(int v, int a) { return (v + a - 1) / a * a; }
 
+struct PendingPrologue {
+  int tensor = -1;
+  std::vector<float> scale, shift;
+  bool relu = false;
+  std::string names;
+};
+
 struct Builder {
   const OnnxModel& m;
   int align;
+  bool consumer_prologue = true;
+  std::map<std::string, PendingPrologue> prologues;   // activated value name -> how to make it on the fly
   Plan plan;
   std::map<std::string, std::vector<int>> consumers;  // value name -> node indices
   std::set<std::string> graph_outputs;
@@ -42,7 +51,7 @@ struct Builder {
   std::vector<PlanLayer> layers;          // creation order; `order` is the execution order
   std::vector<int> order;
 
-  Builder(const OnnxModel& model, int a) : m(model), align(a), absorbed(model.nodes.size(), 0) {
+  Builder(const OnnxModel& model, int a, bool cp) : m(model), align(a), consumer_prologue(cp), absorbed(model.nodes.size(), 0) {
     for (size_t i = 0; i < m.nodes.size(); ++i)
       for (auto& in : m.nodes[i].inputs) consumers[in].push_back(int(i));
     for (auto& o : m.outputs) graph_outputs.insert(o.name);
@@ -115,6 +124,49 @@ struct Builder {
 
   static void pad_to(std::vector<float>& v, size_t n, float fill) { v.resize(n, fill); }
 
+  // "T -> BN [-> ReLU] -> only 1x1, pad-0, group-1 convs": let those convs apply the affine+ReLU to
+  // their operand as it is staged; nothing is materialised.  (With padding this would be wrong: the
+  // conv pads the activated tensor with zeros, not with relu(shift).)
+  bool defer_act_to_consumers(int node_idx) {
+    if (!consumer_prologue) return false;
+    const OnnxNode& bn = m.nodes[size_t(node_idx)];
+    int tid = tensor_of(bn.inputs[0], bn);
+    const PlanTensor src = plan.tensors[size_t(tid)];
+    if (src.vec_f32) return false;
+    // only worth it when the raw tensor is written anyway (someone else reads it); otherwise the
+    // producer can simply write the activated copy instead of the raw one, at the same cost
+    if (!graph_outputs.count(bn.inputs[0]) && consumers[bn.inputs[0]].size() <= 1) return false;
+    std::string outname = bn.outputs[0];
+    int r = sole_consumer(outname, "Relu");
+    if (r >= 0) outname = m.nodes[size_t(r)].outputs[0];
+    if (graph_outputs.count(outname)) return false;
+    auto cit = consumers.find(outname);
+    if (cit == consumers.end() || cit->second.empty()) return false;
+    for (int c : cit->second) {
+      const OnnxNode& n = m.nodes[size_t(c)];
+      if (n.op != "Conv" || n.inputs[0] != outname) return false;
+      for (size_t k = 1; k < n.inputs.size(); ++k)
+        if (n.inputs[k] == outname) return false;
+      auto ks = n.attr_ints("kernel_shape", {});
+      auto pd = n.attr_ints("pads", {0, 0, 0, 0});
+      if (ks.size() != 2 || ks[0] != 1 || ks[1] != 1) return false;
+      for (auto v : pd) if (v != 0) return false;
+      if (n.attr_i("group", 1) != 1) return false;
+    }
+    PendingPrologue pp;
+    pp.tensor = tid;
+    bn_affine(bn, pp.scale, pp.shift);
+    if (int(pp.scale.size()) != src.C) fail("BN '" + bn.name + "': channel count mismatch");
+    pad_to(pp.scale, size_t(src.Cpad), 0.f);
+    pad_to(pp.shift, size_t(src.Cpad), 0.f);
+    pp.relu = r >= 0;
+    pp.names = bn.name + (r >= 0 ? "+" + m.nodes[size_t(r)].name : std::string());
+    absorbed[size_t(node_idx)] = 1;
+    if (r >= 0) absorbed[size_t(r)] = 1;
+    prologues[outname] = std::move(pp);
+    return true;
+  }
+
   // Try to hang "-> BN [-> ReLU]" on tensor `tid` as the producing layer's second output.
   // Returns true (and registers the value names) when done.
   bool fuse_act_into_producer(int node_idx) {
@@ -179,7 +231,11 @@ struct Builder {
 
   void do_conv(int idx) {
     const OnnxNode& n = m.nodes[size_t(idx)];
-    int tin = tensor_of(n.inputs[0], n);
+    const PendingPrologue* pro = nullptr;
+    int tin;
+    auto pit = prologues.find(n.inputs[0]);
+    if (pit != prologues.end()) { pro = &pit->second; tin = pro->tensor; }
+    else tin = tensor_of(n.inputs[0], n);
     const PlanTensor in = plan.tensors[size_t(tin)];
     if (in.vec_f32) fail("Conv '" + n.name + "' on a flattened tensor");
     const auto& w = init(n.inputs[1], "Conv weight");
@@ -201,6 +257,10 @@ struct Builder {
     L.kind = LayerKind::Conv;
     L.name = n.name;
     L.in = tin;
+    if (pro) {
+      L.pre_scale = pro->scale; L.pre_shift = pro->shift; L.pre_relu = pro->relu;
+      L.name = pro->names + "+" + n.name;
+    }
     L.Cin = in.Cpad; L.kh = kh; L.kw = kw; L.stride = stride; L.pad = pad;
     L.macs_per_sample = double(Cout) * Cin * kh * kw * Ho * Wo;
     std::vector<double> scale(size_t(Cout), 1.0);
@@ -281,6 +341,7 @@ struct Builder {
   void do_bn_or_relu(int idx) {
     const OnnxNode& n = m.nodes[size_t(idx)];
     bool is_bn = n.op == "BatchNormalization";
+    if (is_bn && defer_act_to_consumers(idx)) return;
     if (is_bn && fuse_act_into_producer(idx)) return;
     int tin = tensor_of(n.inputs[0], n);
     const PlanTensor in = plan.tensors[size_t(tin)];
@@ -466,8 +527,8 @@ struct Builder {
 
 }  // namespace
 
-Plan build_plan(const OnnxModel& model, int channel_align) {
-  Builder b(model, channel_align);
+Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue) {
+  Builder b(model, channel_align, consumer_prologue);
   return b.run();
 }
 
@@ -489,7 +550,7 @@ std::string Plan::describe() const {
     if (L.kind == LayerKind::Conv)
       os << " k=" << L.kh << "x" << L.kw << " s=" << L.stride << " p=" << L.pad << " cin=" << L.Cin << " cout=" << L.Cout;
     if (L.kind == LayerKind::MaxPool) os << " k=" << L.pool_k << " s=" << L.pool_stride << " p=" << L.pool_pad;
-    os << " relu=" << int(L.relu) << " act_relu=" << int(L.act_relu) << " | " << L.name << "\n";
+    os << " relu=" << int(L.relu) << " act_relu=" << int(L.act_relu) << " pre=" << int(!L.pre_scale.empty()) << " | " << L.name << "\n";
   }
   return os.str();
 }

@@ -7,8 +7,10 @@
 //   Conv -> BN            (BN the only consumer)      : folded into weights + bias
 //   ... -> ReLU           (only consumer)             : epilogue ReLU
 //   ... -> Add(x, other)  (only consumer)             : epilogue residual add
-//   T -> BN -> ReLU       (T made by Conv/MaxPool)    : second epilogue output relu(s*T+t); the raw
-//                                                       T is not written at all if nothing else reads it
+//   T -> BN -> ReLU -> 1x1 convs only              : applied to those convs' A operand while it is
+//                                                       staged in shared memory; no activated copy exists
+//   T -> BN -> ReLU       (T made by Conv/MaxPool)    : otherwise a second epilogue output relu(s*T+t);
+//                                                       the raw T is not written if nothing else reads it
 //   input -> BN           (BN the only consumer)      : applied while re-laying NCHW fp32 -> NHWC
 //   BN -> ReLU -> GlobalAveragePool                    : affine+ReLU applied inside the pooling kernel
 // Anything else falls back to a stand-alone element-wise layer; an operator outside the
@@ -51,6 +53,11 @@ struct PlanLayer {
   // second output / stand-alone affine / pooling prologue
   std::vector<float> act_scale, act_shift;
   bool act_relu = false;
+  // Conv prologue: the input is read as relu?(pre_scale[c] * x + pre_shift[c]) (a BN -> ReLU that sits
+  // between a residual sum and the 1x1 convs that read it, applied while the operand is staged, so the
+  // activated copy of the tensor is never written to memory)
+  std::vector<float> pre_scale, pre_shift;
+  bool pre_relu = false;
   // MaxPool
   int pool_k = 0, pool_stride = 0, pool_pad = 0;
   double macs_per_sample = 0;  // algorithmic multiply-accumulates (Conv/Gemm), for rooflines
@@ -71,6 +78,8 @@ struct Plan {
 
 // channel_align: activations are stored with channels rounded up to this (4 for the fp32 path,
 // 8 for 16-bit paths; the 3-channel network input is always stored as 4).
-Plan build_plan(const OnnxModel& model, int channel_align);
+// consumer_prologue: fuse "T -> BN -> ReLU -> {1x1 pad-0 convs}" into those convs' operand load instead
+// of a second output of T's producer (saves writing and re-reading the activated copy).
+Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue = false);
 
 }  // namespace rn

@@ -124,10 +124,12 @@ int b200rn_time_forward(b200rn_t* h, const float* const* d_inputs, int n_inputs,
  * dtype: 0 fp32 (CUDA-core path), 1 bf16, 2 fp16 (tcgen05 path).  w: fp32 host weights
  * [Cout][kh][kw][Cin]; bias/act_scale/act_shift: fp32 host arrays [Cout] (act_* may be NULL).
  * residual / out / out_act are device NHWC tensors of dtype (any of them may be NULL except that
- * one output must exist). */
+ * one output must exist).  pre_scale / pre_shift (fp32 host arrays [Cin], may be NULL; 1x1 pad-0 convs
+ * only) make the conv read relu?(pre_scale[c]*x + pre_shift[c]) instead of x. */
 int b200rn_conv2d(int dtype, const void* d_in, int B, int H, int W, int Cin, const float* w, const float* bias,
                   int Cout, int kh, int kw, int stride, int pad, int relu, const void* d_residual, void* d_out,
-                  void* d_out_act, const float* act_scale, const float* act_shift, int act_relu);
+                  void* d_out_act, const float* act_scale, const float* act_shift, int act_relu,
+                  const float* pre_scale, const float* pre_shift, int pre_relu);
 /* Same, for the 7x7/2 stem through the tensor-core path: d_in_nchw is fp32 NCHW [B,3,H,W]; the
  * input re-layout (with per-channel scale/shift) and the conv run back to back. */
 int b200rn_stem_conv(int dtype, const float* d_in_nchw, int B, int H, int W, const float* in_scale,

@@ -17,7 +17,7 @@ TOL = {0: (2e-5, 2e-5), 1: (1.2e-2, 1.2e-2), 2: (1.5e-3, 1.5e-3)}
 
 
 def conv_case(dtype, B, H, W, Cin, Cout, k, stride, pad, relu=0, residual=False, want_out=True, want_act=False,
-              act_relu=1, seed=0):
+              act_relu=1, seed=0, prologue=False):
     """Runs b200rn_conv2d on random data; returns dict(err_out, err_act, ...) vs a float64 CPU conv."""
     g = torch.Generator().manual_seed(seed)
     tdt = TORCH_DT[dtype]
@@ -28,8 +28,14 @@ def conv_case(dtype, B, H, W, Cin, Cout, k, stride, pad, relu=0, residual=False,
     res = torch.randn(B, Cout, Ho, Wo, generator=g).to(tdt) if residual else None
     s2 = torch.rand(Cout, generator=g) + 0.5
     t2 = torch.randn(Cout, generator=g) * 0.3
+    ps = torch.rand(Cin, generator=g) + 0.5
+    pt = torch.randn(Cin, generator=g) * 0.3
+    xin = x.double()
+    if prologue:
+        # what the kernel feeds the MMA: relu(ps*x+pt) rounded back to the storage type
+        xin = (x.float() * ps.view(1, -1, 1, 1) + pt.view(1, -1, 1, 1)).clamp_min(0).to(tdt).double()
     # expected (float64 on the rounded operands)
-    y = F.conv2d(x.double(), w.double(), bias.double(), stride=stride, padding=pad)
+    y = F.conv2d(xin, w.double(), bias.double(), stride=stride, padding=pad)
     if relu:
         y = y.clamp_min(0)
     if residual:
@@ -45,11 +51,13 @@ def conv_case(dtype, B, H, W, Cin, Cout, k, stride, pad, relu=0, residual=False,
     w_khwc = np.ascontiguousarray(w.float().permute(0, 2, 3, 1).numpy())   # [Cout][kh][kw][Cin]
     b_np = bias.numpy().astype(np.float32)
     s_np, t_np = s2.numpy().astype(np.float32), t2.numpy().astype(np.float32)
+    ps_np, pt_np = ps.numpy().astype(np.float32), pt.numpy().astype(np.float32)
     torch.cuda.synchronize()
     rc = lib.b200rn_conv2d(dtype, d_x.data_ptr(), B, H, W, Cin, pkg.fptr(w_khwc), pkg.fptr(b_np), Cout, k, k, stride,
                            pad, relu, d_res.data_ptr() if residual else None,
                            d_out.data_ptr() if want_out else None, d_act.data_ptr() if want_act else None,
-                           pkg.fptr(s_np), pkg.fptr(t_np), act_relu)
+                           pkg.fptr(s_np), pkg.fptr(t_np), act_relu,
+                           pkg.fptr(ps_np) if prologue else None, pkg.fptr(pt_np) if prologue else None, 1)
     out = {"rc": rc, "msg": lib.b200rn_global_error().decode() if rc else ""}
     if rc:
         return out
@@ -118,4 +126,8 @@ CONV_CASES = [
     ("1x1 512->2048 @7 res act-only", dict(B=2, H=7, W=7, Cin=512, Cout=2048, k=1, stride=1, pad=0, residual=True,
                                            want_out=False, want_act=True)),
     ("3x3 s2 512->512 @14 B33", dict(B=33, H=14, W=14, Cin=512, Cout=512, k=3, stride=2, pad=1, relu=1)),
+    ("1x1 256->64 @56 prologue", dict(B=2, H=56, W=56, Cin=256, Cout=64, k=1, stride=1, pad=0, relu=1, prologue=True)),
+    ("1x1 s2 512->1024 @28 prologue", dict(B=3, H=28, W=28, Cin=512, Cout=1024, k=1, stride=2, pad=0, prologue=True)),
+    ("1x1 1024->256 @14 prologue B40", dict(B=40, H=14, W=14, Cin=1024, Cout=256, k=1, stride=1, pad=0, relu=1, prologue=True)),
+    ("3x3 s1 256->256 @14 B64 (N=256 tiles)", dict(B=64, H=14, W=14, Cin=256, Cout=256, k=3, stride=1, pad=1, relu=1)),
 ]

