@@ -163,6 +163,32 @@ def reference_arm(args):
     return 0
 
 
+def whole_job_value(world, steps, batch, max_ms):
+    """images/s of the whole job: every rank ran `steps` batches; time is the max over ranks."""
+    return world * steps * batch / (max_ms * 1e-3)
+
+
+def dry_run_dist(args):
+    """No GPU: each rank pretends its K steps took (10 + rank) ms and the ranks agree on the aggregate."""
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        dist.init_process_group("gloo")
+        dist.barrier()
+    t = torch.tensor([10.0 + rank], dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps({"metric": METRIC, "unit": UNIT, "dry_run": True, "n_gpus": world, "steps": args.steps,
+                          "max_ms": float(t.item()), "value": whole_job_value(world, args.steps, args.batch, float(t.item())),
+                          "scaling": "weak"}), flush=True)
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -173,10 +199,14 @@ def main():
     ap.add_argument("--mode", default="fp16", choices=["fp16", "bf16", "exact"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layers-out", default="", help="write the per-layer roofline table (JSON) here")
+    ap.add_argument("--dry-run-dist", action="store_true",
+                    help="CPU-only check of the multi-rank plumbing (gloo): barrier, max-over-ranks, one line from rank 0")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
         return reference_arm(args)
+    if args.dry_run_dist:
+        return dry_run_dist(args)
 
     import numpy as np
     import torch
@@ -226,7 +256,7 @@ def main():
     ms = eng.time_forward(ptrs, B, K)                     # EXACTLY K steps, CUDA events on the compute stream
     barrier()
     ms = max_over_ranks(ms)
-    value = world * K * B / (ms * 1e-3)
+    value = whole_job_value(world, K, B, ms)
 
     # ---- end to end through the C ABI with pinned host buffers ------------------------------------
     in_bytes, out_bytes = B * in_elems * 4, B * eng.out_elems * 4
