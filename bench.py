@@ -222,6 +222,7 @@ def main():
     dist = None
     if world > 1:
         import torch.distributed as dist
+        os.environ["NCCL_DEBUG"] = "WARN"        # keep NCCL's version banner off stdout: rank 0 prints ONE line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
