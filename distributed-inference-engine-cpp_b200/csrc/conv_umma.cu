@@ -21,6 +21,7 @@
 #include <cuda_fp16.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -41,9 +42,11 @@ constexpr int kChunkBytes = kTileM * 128;  // one 64-channel output chunk of a t
 struct UmmaParams {
   int num_k_iters, cblks, kw, stride, pad, stem;
   int bw, bh, bn, tiles_w, tiles_h;
-  int n_tiles, num_stages, total_tiles, raw_bufs;
+  int n_tiles, num_stages, total_tiles, raw_bufs, act_bufs;
+  int relaxed_store_wait;   // staging is double-buffered: the previous tile's TMA stores may still be reading
   int has_res, has_out, has_act, relu, act_relu;
   int has_pre, pre_relu, cin;
+  int b_stationary;   // the CTA's whole weight slab (all K blocks of its N tile) is loaded once and stays in smem
   uint32_t a_bytes, b_bytes, rows;
   const float* bias;
   const float* act_scale;
@@ -111,6 +114,10 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, uint32_t src,
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void tma_store_wait_read_pending() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kPending) : "memory");
+}
 
 __device__ __forceinline__ void tmem_alloc(uint32_t slot_smem, uint32_t cols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot_smem), "r"(cols) : "memory");
@@ -236,16 +243,18 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr int kMmaPerBlock = KB / 32;        // UMMA_K = 16 elements = 32 bytes
   constexpr uint32_t A_BYTES = kTileM * KB;
   constexpr uint32_t B_BYTES = BLOCK_N * KB;
-  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  // a pipeline stage holds an A tile and, unless the weights are stationary, the matching B tile
+  const uint32_t STAGE_BYTES = p.b_stationary ? A_BYTES : A_BYTES + B_BYTES;
   constexpr uint32_t RAW_BYTES = kChunks * kChunkBytes;   // one tile's raw / residual staging
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int S = p.num_stages;
   uint8_t* pipe = smem;
-  uint8_t* rawbuf = pipe + S * STAGE_BYTES;
+  uint8_t* bstat = pipe + S * STAGE_BYTES;      // [num_k_iters x B tile] when b_stationary
+  uint8_t* rawbuf = bstat + (p.b_stationary ? p.num_k_iters * B_BYTES : 0);
   uint8_t* actbuf = rawbuf + ((p.has_out || p.has_res) ? p.raw_bufs * RAW_BYTES : 0);
-  uint8_t* tail = actbuf + (p.has_act ? RAW_BYTES : 0);
+  uint8_t* tail = actbuf + (p.has_act ? p.act_bufs * RAW_BYTES : 0);
   float* s_bias = reinterpret_cast<float*>(tail);
   float* s_scale = s_bias + BLOCK_N;
   float* s_shift = s_scale + BLOCK_N;
@@ -259,7 +268,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* res_full = tmem_empty + 2;        // [2]  TMA -> epilogue
   uint64_t* res_empty = res_full + 2;         // [2]  epilogue -> TMA
   uint64_t* xf_bar = res_empty + 2;           // [S]  transform warps -> MMA (128 arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xf_bar + S);
+  uint64_t* bstat_bar = xf_bar + S;           // [1]  stationary weights landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bstat_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool f_relu = EPI >= 0 ? bool(EPI & EPI_RELU) : bool(p.relu);
@@ -285,6 +295,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_init(smem_u32(&res_full[i]), 1);
       mbar_init(smem_u32(&res_empty[i]), 1);
     }
+    mbar_init(smem_u32(bstat_bar), 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * BLOCK_N);
@@ -304,13 +315,21 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int stage = 0;
       uint32_t phase = 0;
       int i = 0;
+      if (p.b_stationary && int(blockIdx.x) < p.total_tiles) {
+        // gridDim.x is a multiple of n_tiles, so this CTA only ever sees one N tile: fetch its weights once
+        const int col0 = (int(blockIdx.x) % p.n_tiles) * BLOCK_N;
+        const uint32_t bb = smem_u32(bstat_bar);
+        mbar_expect_tx(bb, uint32_t(p.num_k_iters) * p.b_bytes);
+        for (int it = 0; it < p.num_k_iters; ++it)
+          tma_load_2d(smem_u32(bstat + it * B_BYTES), &tmW, bb, it * (KB / 2), col0);
+      }
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++i) {
         const TileCoord tc = decode_tile(p, tile, BLOCK_N);
         for (int it = 0; it < p.num_k_iters; ++it) {
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
           const uint32_t fb = smem_u32(&full_bar[stage]);
           const uint32_t a_dst = smem_u32(pipe + stage * STAGE_BYTES);
-          mbar_expect_tx(fb, p.a_bytes + p.b_bytes);
+          mbar_expect_tx(fb, p.b_stationary ? p.a_bytes : p.a_bytes + p.b_bytes);
           if (p.stem) {
             tma_load_5d(a_dst, &tmA, fb, 0, tc.w0, it & 1, tc.h0 + (it >> 1), tc.n0);
           } else {
@@ -318,7 +337,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int ky = tap / p.kw, kx = tap - ky * p.kw;
             tma_load_4d(a_dst, &tmA, fb, cb * 64, tc.w0 * p.stride - p.pad + kx, tc.h0 * p.stride - p.pad + ky, tc.n0);
           }
-          tma_load_2d(a_dst + A_BYTES, &tmW, fb, it * (KB / 2), tc.col0);
+          if (!p.b_stationary) tma_load_2d(a_dst + A_BYTES, &tmW, fb, it * (KB / 2), tc.col0);
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
         if (p.has_res) {
@@ -340,6 +359,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int stage = 0;
     uint32_t phase = 0;
     int i = 0;
+    if (p.b_stationary && int(blockIdx.x) < p.total_tiles) mbar_wait(smem_u32(bstat_bar), 0);
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++i) {
       const int buf = i & 1;
       mbar_wait(smem_u32(&tmem_empty[buf]), ((i >> 1) & 1) ^ 1);   // epilogue drained this accumulator
@@ -350,7 +370,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tc_fence_after();
         if (elect_one()) {
           const uint32_t a_addr = smem_u32(pipe + stage * STAGE_BYTES);
-          const uint32_t b_addr = a_addr + A_BYTES;
+          const uint32_t b_addr = p.b_stationary ? smem_u32(bstat + it * B_BYTES) : a_addr + A_BYTES;
 #pragma unroll
           for (int k = 0; k < kMmaPerBlock; ++k) {
             const uint64_t da = make_smem_desc<KB>(a_addr + k * 32);
@@ -430,7 +450,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
       if (store_thread && i > 0) {
-        tma_store_wait_read();              // previous tile's stores have read their staging buffers
+        // staging buffers about to be rewritten must have been read by their TMA stores: all of them, or --
+        // with double-buffered staging -- all but the previous tile's kChunks store groups
+        if (p.relaxed_store_wait) tma_store_wait_read_pending<kChunks>();
+        else tma_store_wait_read();
         if (f_res) mbar_arrive(smem_u32(&res_empty[(p.raw_bufs == 2) ? ((i - 1) & 1) : 0]));
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
@@ -449,7 +472,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           mbar_arrive(smem_u32(&tmem_empty[buf]));
         }
         uint8_t* raw_stage = raw_tile + c * kChunkBytes;
-        uint8_t* act_stage = actbuf + c * kChunkBytes;
+        uint8_t* act_stage = actbuf + ((p.act_bufs == 2) ? (i & 1) * RAW_BYTES : 0) + c * kChunkBytes;
         uint4* raw_row = reinterpret_cast<uint4*>(raw_stage + row * 128);
         uint4* act_row = reinterpret_cast<uint4*>(act_stage + row * 128);
 #pragma unroll
@@ -666,10 +689,10 @@ static void plan_geometry(UmmaConvPlan& pl) {
   // N-tile width: minimise (rounds over the SMs) x (operand bytes staged per K block), i.e. the
   // shared-memory fill traffic per SM, among the widths that divide Cout and leave >= 3 stages.
   const uint32_t budget = 227u * 1024;
-  auto fixed_bytes = [&](int bn, int nb) {
+  auto fixed_bytes = [&](int bn, int nb, int nab = 1) {
     const uint32_t raw_bytes = uint32_t(bn / 64) * kChunkBytes;
-    return 1024u + ((p.has_out || p.has_res) ? uint32_t(nb) * raw_bytes : 0u) + (p.has_act ? raw_bytes : 0u) +
-           3u * uint32_t(bn) * 4 + (p.has_pre ? 8u * uint32_t(g.Cin) : 0u) + 8u * (3 * 8 + 8) + 64;
+    return 1024u + ((p.has_out || p.has_res) ? uint32_t(nb) * raw_bytes : 0u) + (p.has_act ? uint32_t(nab) * raw_bytes : 0u) +
+           3u * uint32_t(bn) * 4 + (p.has_pre ? 8u * uint32_t(g.Cin) : 0u) + 8u * (3 * 8 + 9) + 64;
   };
   auto stage_bytes_of = [&](int bn) { return uint32_t(kTileM * pl.kb + bn * pl.kb); };
   int best_bn = 64;
@@ -697,12 +720,35 @@ static void plan_geometry(UmmaConvPlan& pl) {
   // double-buffer the residual/raw staging when a residual is prefetched and it still leaves 3 stages
   p.raw_bufs = (p.has_res && budget > fixed_bytes(pl.block_n, 2) &&
                 (budget - fixed_bytes(pl.block_n, 2)) / stage_bytes >= 3) ? 2 : 1;
-  const uint32_t fixed = fixed_bytes(pl.block_n, p.raw_bufs);
-  int stages = int((budget - fixed) / stage_bytes);
+  p.act_bufs = 1;
+  p.relaxed_store_wait = 0;
+  // no residual: double-buffer the output staging instead, so a tile's epilogue never waits for the previous
+  // tile's TMA stores to finish reading (matters for the many-small-tiles layers: stem, 64-channel convs)
+  if (!p.has_res && budget > fixed_bytes(pl.block_n, 2, 2) && (budget - fixed_bytes(pl.block_n, 2, 2)) / stage_bytes >= 3) {
+    p.raw_bufs = 2; p.act_bufs = 2; p.relaxed_store_wait = 1;
+  }
+  uint32_t fixed = fixed_bytes(pl.block_n, p.raw_bufs, p.act_bufs);
+  pl.grid = std::min(p.total_tiles, sms);
+  // Stationary weights: when the N tile's whole weight slab is small, keep it in shared memory for the CTA's
+  // lifetime instead of re-fetching a B tile with every A tile (the grid is trimmed to a multiple of n_tiles so
+  // that a CTA always works on the same N tile).
+  const uint32_t slab = uint32_t(p.num_k_iters) * p.b_bytes;
+  const uint32_t a_only = uint32_t(kTileM * pl.kb);
+  const int grid_bs = (pl.grid / p.n_tiles) * p.n_tiles;
+  const char* bs_env = std::getenv("B200RN_BSTAT");
+  p.b_stationary = 0;
+  uint32_t stage_eff = stage_bytes;
+  if (!(bs_env && bs_env[0] == '0') && slab <= 72u * 1024 && grid_bs >= 1 && grid_bs * 8 >= pl.grid * 7 &&
+      p.total_tiles >= 4 * pl.grid && budget > fixed + slab && (budget - fixed - slab) / a_only >= 3) {
+    p.b_stationary = 1;
+    fixed += slab;
+    stage_eff = a_only;
+    pl.grid = grid_bs;
+  }
+  int stages = int((budget - fixed) / stage_eff);
   stages = std::max(2, std::min(stages, 8));
   p.num_stages = stages;
-  pl.smem_bytes = fixed + uint32_t(stages) * stage_bytes;
-  pl.grid = std::min(p.total_tiles, sms);
+  pl.smem_bytes = fixed + uint32_t(stages) * stage_eff;
 }
 
 template <typename T, int BLOCK_N, int KB, int EPI>
