@@ -46,6 +46,7 @@ struct UmmaParams {
   int relaxed_store_wait;   // staging is double-buffered: the previous tile's TMA stores may still be reading
   int has_res, has_out, has_act, relu, act_relu;
   int has_pre, pre_relu, cin;
+  int dbg_ashift, dbg_baseoff;   // descriptor experiment (B200RN_DBG_ASHIFT / B200RN_DBG_BASEOFF), 0 in production
   int b_stationary;   // the CTA's whole weight slab (all K blocks of its N tile) is loaded once and stays in smem
   uint32_t a_bytes, b_bytes, rows;
   const float* bias;
@@ -354,34 +355,34 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one elected thread) =====
+    // ===== MMA issuer: one elected thread runs the whole loop (waits, tcgen05.mma, commits) =====
     constexpr uint32_t idesc = make_idesc<T, BLOCK_N>();
-    int stage = 0;
-    uint32_t phase = 0;
-    int i = 0;
-    if (p.b_stationary && int(blockIdx.x) < p.total_tiles) mbar_wait(smem_u32(bstat_bar), 0);
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++i) {
-      const int buf = i & 1;
-      mbar_wait(smem_u32(&tmem_empty[buf]), ((i >> 1) & 1) ^ 1);   // epilogue drained this accumulator
-      tc_fence_after();
-      const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
-      for (int it = 0; it < p.num_k_iters; ++it) {
-        mbar_wait(smem_u32(p.has_pre ? &xf_bar[stage] : &full_bar[stage]), phase);
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int i = 0;
+      if (p.b_stationary && int(blockIdx.x) < p.total_tiles) mbar_wait(smem_u32(bstat_bar), 0);
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++i) {
+        const int buf = i & 1;
+        mbar_wait(smem_u32(&tmem_empty[buf]), ((i >> 1) & 1) ^ 1);   // epilogue drained this accumulator
         tc_fence_after();
-        if (elect_one()) {
+        const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
+        for (int it = 0; it < p.num_k_iters; ++it) {
+          mbar_wait(smem_u32(p.has_pre ? &xf_bar[stage] : &full_bar[stage]), phase);
+          tc_fence_after();
           const uint32_t a_addr = smem_u32(pipe + stage * STAGE_BYTES);
           const uint32_t b_addr = p.b_stationary ? smem_u32(bstat + it * B_BYTES) : a_addr + A_BYTES;
 #pragma unroll
           for (int k = 0; k < kMmaPerBlock; ++k) {
-            const uint64_t da = make_smem_desc<KB>(a_addr + k * 32);
+            uint64_t da = make_smem_desc<KB>(a_addr + k * 32 + p.dbg_ashift * 128);
+            if (p.dbg_baseoff) da |= uint64_t(((a_addr + p.dbg_ashift * 128) >> 7) & 7) << 49;
             const uint64_t db = make_smem_desc<KB>(b_addr + k * 32);
             umma_f16(tmem_d, da, db, idesc, (it | k) != 0 ? 1u : 0u);
           }
           umma_commit(smem_u32(&empty_bar[stage]));                               // frees the smem slot
           if (it == p.num_k_iters - 1) umma_commit(smem_u32(&tmem_full[buf]));     // accumulator complete
+          if (++stage == S) { stage = 0; phase ^= 1; }
         }
-        __syncwarp();
-        if (++stage == S) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp >= 2 + kEpiWarps) {
@@ -531,6 +532,242 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
 }
 
+// ---- 3x3 / stride 1 / pad 1 with ONE halo load per tile ------------------------------------------
+// For the 64- and 128-channel 3x3 layers the generic kernel is bound by the shared-memory fill rate: it
+// fetches the A tile nine times (once per filter tap).  Here a tile is 14 x 8 output pixels of one image,
+// laid out as 8 rows of 16 (two junk columns per row), so M row r = y*16 + x.  The (14+2) x (8+2) input
+// patch of one 64-channel block is fetched ONCE (TMA zero-fills outside the image = the conv's padding) as
+// 160 rows of 128 bytes, and the A operand of tap (ky,kx) is simply that buffer read from row ky*16+kx on:
+// row r of the tile then reads patch row (y+ky)*16 + (x+kx).  This works because the tensor core applies the
+// 128-byte swizzle to absolute shared-memory addresses, so a descriptor may start at any 128-byte row
+// (measured: tools/dbg_ashift.py).  Outputs in the junk columns are computed and never stored.
+// Weights stay in shared memory for the CTA's lifetime when the slab fits, else stream through their own ring.
+constexpr int kHaloBW = 14, kHaloBH = 8, kHaloPW = 16, kHaloPH = 10;
+constexpr uint32_t kHaloLoadBytes = kHaloPW * kHaloPH * 128;     // 160 rows
+constexpr uint32_t kHaloStageBytes = 21 * 1024;                   // + junk rows read by the junk columns
+
+struct HaloParams {
+  int cblks, n_tiles, total_tiles, tiles_w, tiles_h;
+  int halo_stages, b_stages, b_stationary, relu;
+  const float* bias;
+};
+
+template <typename T, int BLOCK_N>
+__global__ void __launch_bounds__(kBaseThreads, 1)
+conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_constant__ CUtensorMap tmW,
+                    const __grid_constant__ CUtensorMap tmOutRow, const HaloParams p) {
+  constexpr int kChunks = BLOCK_N / 64;
+  constexpr uint32_t B_BYTES = BLOCK_N * 128;
+  constexpr uint32_t OUT_BYTES = kChunks * kChunkBytes;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int HS = p.halo_stages, SB = p.b_stages;
+  const int kblocks = 9 * p.cblks;
+  uint8_t* halo = smem;
+  uint8_t* bbuf = halo + HS * kHaloStageBytes;                     // stationary slab or ring of SB tiles
+  uint8_t* outbuf = bbuf + (p.b_stationary ? kblocks : SB) * B_BYTES;  // 2 x [kChunks x 16 KB]
+  float* s_bias = reinterpret_cast<float*>(outbuf + 2 * OUT_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_bias + BLOCK_N);
+  uint64_t* halo_full = bars;                 // [HS]
+  uint64_t* halo_empty = halo_full + HS;      // [HS]
+  uint64_t* b_full = halo_empty + HS;         // [SB] (b_full[0] doubles as "slab landed" when stationary)
+  uint64_t* b_empty = b_full + SB;            // [SB]
+  uint64_t* tmem_full = b_empty + SB;         // [2]
+  uint64_t* tmem_empty = tmem_full + 2;       // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int my_tiles = (int(blockIdx.x) < p.total_tiles) ? (p.total_tiles - 1 - int(blockIdx.x)) / int(gridDim.x) + 1 : 0;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmHalo);
+    prefetch_tmap(&tmW);
+    prefetch_tmap(&tmOutRow);
+    for (int i = 0; i < HS; ++i) { mbar_init(smem_u32(&halo_full[i]), 1); mbar_init(smem_u32(&halo_empty[i]), 1); }
+    for (int i = 0; i < SB; ++i) { mbar_init(smem_u32(&b_full[i]), 1); mbar_init(smem_u32(&b_empty[i]), 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&tmem_full[i]), 1); mbar_init(smem_u32(&tmem_empty[i]), kEpiThreads); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * BLOCK_N);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  auto tile_coord = [&](int tile, int& x0, int& y0, int& n, int& col0) {
+    const int nt = tile % p.n_tiles;
+    int mt = tile / p.n_tiles;
+    const int tw = mt % p.tiles_w; mt /= p.tiles_w;
+    const int th = mt % p.tiles_h;
+    n = mt / p.tiles_h;
+    x0 = tw * kHaloBW; y0 = th * kHaloBH; col0 = nt * BLOCK_N;
+  };
+
+  if (warp == 0) {
+    // ===== TMA producer: halo patches run ahead of the weight tiles =====
+    if (elect_one() && my_tiles > 0) {
+      const int Q = my_tiles * p.cblks;         // items: (tile, channel block)
+      if (p.b_stationary) {
+        const int col0 = (int(blockIdx.x) % p.n_tiles) * BLOCK_N;
+        mbar_expect_tx(smem_u32(&b_full[0]), uint32_t(kblocks) * B_BYTES);
+        for (int kb = 0; kb < kblocks; ++kb)
+          tma_load_2d(smem_u32(bbuf + kb * B_BYTES), &tmW, smem_u32(&b_full[0]), kb * 64, col0);
+      }
+      auto issue_halo = [&](int hq) {
+        const int tile = int(blockIdx.x) + (hq / p.cblks) * int(gridDim.x);
+        const int cb = hq % p.cblks;
+        int x0, y0, n, col0;
+        tile_coord(tile, x0, y0, n, col0);
+        const int slot = hq % HS;
+        const uint32_t fb = smem_u32(&halo_full[slot]);
+        mbar_expect_tx(fb, kHaloLoadBytes);
+        tma_load_4d(smem_u32(halo + slot * kHaloStageBytes), &tmHalo, fb, cb * 64, x0 - 1, y0 - 1, n);
+      };
+      int hq = 0, bstage = 0;
+      uint32_t bphase = 0;
+      for (int q = 0; q < Q; ++q) {
+        // keep up to HS patches in flight without ever blocking on a slot that is still being read
+        while (hq < Q && hq < q + HS) {
+          const int slot = hq % HS;
+          const uint32_t par = (uint32_t(hq / HS) & 1) ^ 1;
+          if (hq == q) mbar_wait(smem_u32(&halo_empty[slot]), par);               // this one is needed now
+          else if (hq >= HS && !mbar_try_wait(smem_u32(&halo_empty[slot]), par)) break;
+          issue_halo(hq);
+          ++hq;
+        }
+        if (!p.b_stationary) {
+          const int tile = int(blockIdx.x) + (q / p.cblks) * int(gridDim.x);
+          const int cb = q % p.cblks;
+          int x0, y0, n, col0;
+          tile_coord(tile, x0, y0, n, col0);
+          for (int tap = 0; tap < 9; ++tap) {
+            mbar_wait(smem_u32(&b_empty[bstage]), bphase ^ 1);
+            const uint32_t fb = smem_u32(&b_full[bstage]);
+            mbar_expect_tx(fb, B_BYTES);
+            tma_load_2d(smem_u32(bbuf + bstage * B_BYTES), &tmW, fb, (tap * p.cblks + cb) * 64, col0);
+            if (++bstage == SB) { bstage = 0; bphase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: one elected thread =====
+    constexpr uint32_t idesc = make_idesc<T, BLOCK_N>();
+    if (elect_one()) {
+      if (p.b_stationary && my_tiles > 0) mbar_wait(smem_u32(&b_full[0]), 0);
+      int q = 0, bstage = 0;
+      uint32_t bphase = 0;
+      for (int i = 0; i < my_tiles; ++i) {
+        const int buf = i & 1;
+        mbar_wait(smem_u32(&tmem_empty[buf]), ((i >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
+        for (int cb = 0; cb < p.cblks; ++cb, ++q) {
+          const int slot = q % HS;
+          mbar_wait(smem_u32(&halo_full[slot]), uint32_t(q / HS) & 1);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(halo + slot * kHaloStageBytes);
+#pragma unroll 1
+          for (int ky = 0; ky < 3; ++ky) {
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+              const int tap = ky * 3 + kx;
+              uint32_t b_addr;
+              if (p.b_stationary) {
+                b_addr = smem_u32(bbuf + (tap * p.cblks + cb) * B_BYTES);
+              } else {
+                mbar_wait(smem_u32(&b_full[bstage]), bphase);
+                tc_fence_after();
+                b_addr = smem_u32(bbuf + bstage * B_BYTES);
+              }
+              const uint32_t a_addr = a_base + uint32_t(ky * kHaloPW + kx) * 128;   // row-shifted view of the patch
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma_f16(tmem_d, make_smem_desc<128>(a_addr + k * 32), make_smem_desc<128>(b_addr + k * 32), idesc,
+                         (cb | tap | k) != 0 ? 1u : 0u);
+              if (!p.b_stationary) {
+                umma_commit(smem_u32(&b_empty[bstage]));
+                if (++bstage == SB) { bstage = 0; bphase ^= 1; }
+              }
+            }
+          }
+          umma_commit(smem_u32(&halo_empty[slot]));
+          if (cb == p.cblks - 1) umma_commit(smem_u32(&tmem_full[buf]));
+        }
+      }
+    }
+  } else {
+    // ===== epilogue: bias + ReLU; the 14 valid pixels of each row are packed densely, one TMA store per chunk =====
+    const int q4 = warp & 3;
+    const int g = (warp - 2) >> 2;
+    const int row = q4 * 32 + lane;                       // TMEM lane = y*16 + x
+    const bool valid = (row & 15) < kHaloBW;              // x = 14, 15 are the junk columns
+    const int drow = (row >> 4) * kHaloBW + (row & 15);   // dense staging row y*14 + x
+    const int sw = drow & 7;
+    const int et = threadIdx.x - 64;
+    const bool store_thread = (warp == 2 && lane == 0);
+    int cur_ntile = -1;
+    for (int i = 0; i < my_tiles; ++i) {
+      const int tile = int(blockIdx.x) + i * int(gridDim.x);
+      int x0, y0, n, col0;
+      tile_coord(tile, x0, y0, n, col0);
+      const int buf = i & 1;
+      if (tile % p.n_tiles != cur_ntile) {
+        cur_ntile = tile % p.n_tiles;
+        for (int k = et; k < BLOCK_N; k += kEpiThreads) s_bias[k] = __ldg(p.bias + col0 + k);
+      }
+      if (store_thread && i > 0) tma_store_wait_read_pending<kChunks>();   // tile i-2's staging is free again
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      mbar_wait(smem_u32(&tmem_full[buf]), (i >> 1) & 1);
+      tc_fence_after();
+      uint8_t* out_tile = outbuf + buf * OUT_BYTES;
+#pragma unroll 1
+      for (int c = 0; c < kChunks; ++c) {
+        uint32_t acc[32];
+        tmem_ld_32x32b_x32(tmem_base + (uint32_t(q4 * 32) << 16) + uint32_t(buf * BLOCK_N + c * 64 + g * 32), acc);
+        tmem_ld_wait();
+        if (c == kChunks - 1) {
+          tc_fence_before();
+          mbar_arrive(smem_u32(&tmem_empty[buf]));
+        }
+        uint8_t* stage = out_tile + c * kChunkBytes;
+        uint4* out_row = reinterpret_cast<uint4*>(stage + drow * 128);
+        if (valid) {
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const int j = g * 4 + jj;
+            const int col = c * 64 + j * 8;
+            const float4 b0 = *reinterpret_cast<const float4*>(s_bias + col);
+            const float4 b1 = *reinterpret_cast<const float4*>(s_bias + col + 4);
+            float v[8];
+            v[0] = __uint_as_float(acc[jj * 8 + 0]) + b0.x; v[1] = __uint_as_float(acc[jj * 8 + 1]) + b0.y;
+            v[2] = __uint_as_float(acc[jj * 8 + 2]) + b0.z; v[3] = __uint_as_float(acc[jj * 8 + 3]) + b0.w;
+            v[4] = __uint_as_float(acc[jj * 8 + 4]) + b1.x; v[5] = __uint_as_float(acc[jj * 8 + 5]) + b1.y;
+            v[6] = __uint_as_float(acc[jj * 8 + 6]) + b1.z; v[7] = __uint_as_float(acc[jj * 8 + 7]) + b1.w;
+            if (p.relu) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+            }
+            out_row[j ^ sw] = make_uint4(pack2<T>(v[0], v[1]), pack2<T>(v[2], v[3]), pack2<T>(v[4], v[5]), pack2<T>(v[6], v[7]));
+          }
+        }
+        fence_proxy_async_smem();
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (store_thread) {
+          tma_store_4d(&tmOutRow, smem_u32(stage), col0 + c * 64, x0, y0, n);   // box {64 ch, 14, 8, 1}
+          tma_store_commit();
+        }
+      }
+    }
+    if (store_thread) tma_store_wait_read();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
+}
+
 // ---- host side --------------------------------------------------------------------------------
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -597,6 +834,8 @@ struct UmmaConvPlan {
   CUtensorMap tmA, tmW, tmRes, tmOut, tmAct;
   uint32_t smem_bytes;
   int grid;
+  int halo = 0;           // 3x3/s1/p1 layer routed to conv3x3_halo_kernel (tmA = patch map, tmOut = row-store map)
+  HaloParams hp;
 };
 
 bool umma_conv_supported(const ConvGeom& g, int stem_mode, char* why, size_t cap) {
@@ -782,8 +1021,27 @@ static cudaError_t launch_epi(const UmmaConvPlan* pl, cudaStream_t s) {
   }
 }
 
+template <typename T, int BLOCK_N>
+static cudaError_t launch_halo(const UmmaConvPlan* pl, cudaStream_t s) {
+  auto kern = conv3x3_halo_kernel<T, BLOCK_N>;
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    configured_device = dev;
+  }
+  kern<<<pl->grid, kBaseThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmOut, pl->hp);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
   const bool bf = pl->dt == DType::BF16;
+  if (pl->halo) {
+    if (pl->block_n == 64) return bf ? launch_halo<__nv_bfloat16, 64>(pl, s) : launch_halo<__half, 64>(pl, s);
+    return bf ? launch_halo<__nv_bfloat16, 128>(pl, s) : launch_halo<__half, 128>(pl, s);
+  }
   if (pl->kb == 64) return bf ? launch_epi<__nv_bfloat16, 64, 64>(pl, s) : launch_epi<__half, 64, 64>(pl, s);
   if (pl->block_n == 64) return bf ? launch_epi<__nv_bfloat16, 64, 128>(pl, s) : launch_epi<__half, 64, 128>(pl, s);
   if (pl->block_n == 128) return bf ? launch_epi<__nv_bfloat16, 128, 128>(pl, s) : launch_epi<__half, 128, 128>(pl, s);
@@ -807,9 +1065,67 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   p.relu = e.relu; p.act_relu = e.act_relu;
   p.bias = e.bias; p.act_scale = e.act_scale; p.act_shift = e.act_shift;
   p.has_pre = e.pre_scale != nullptr; p.pre_relu = e.pre_relu; p.cin = g.Cin;
+  if (const char* v = std::getenv("B200RN_DBG_ASHIFT")) p.dbg_ashift = std::atoi(v);
+  if (const char* v = std::getenv("B200RN_DBG_BASEOFF")) p.dbg_baseoff = std::atoi(v);
   p.pre_scale = e.pre_scale; p.pre_shift = e.pre_shift;
   if (p.has_pre && (stem_mode || g.kh != 1 || g.kw != 1 || g.pad != 0)) { delete pl; return failmsg("operand prologue needs a 1x1, pad-0 conv"); }
   if (!p.has_out && !p.has_act) { delete pl; return failmsg("conv with no output"); }
+  {
+    // 3x3 / stride 1 / pad 1 on 64 or 128 input channels with a plain (bias, ReLU) epilogue: halo kernel
+    const char* henv = std::getenv("B200RN_HALO");
+    if (!(henv && henv[0] == '0') && !stem_mode && g.kh == 3 && g.kw == 3 && g.stride == 1 && g.pad == 1 &&
+        (g.Cin == 64 || g.Cin == 128) && g.Wo >= kHaloBW && p.has_out && !p.has_res && !p.has_act && !p.has_pre) {
+      HaloParams& hp = pl->hp;
+      std::memset(&hp, 0, sizeof hp);
+      pl->halo = 1;
+      pl->kb = 128;
+      pl->block_n = (g.Cout % 128 == 0) ? 128 : 64;
+      hp.cblks = g.Cin / 64;
+      hp.n_tiles = g.Cout / pl->block_n;
+      hp.tiles_w = (g.Wo + kHaloBW - 1) / kHaloBW;
+      hp.tiles_h = (g.Ho + kHaloBH - 1) / kHaloBH;
+      hp.total_tiles = hp.tiles_w * hp.tiles_h * g.B * hp.n_tiles;
+      hp.relu = e.relu;
+      hp.bias = e.bias;
+      const int sms = sm_count();
+      int grid = std::min(hp.total_tiles, sms);
+      grid = std::max(hp.n_tiles, (grid / hp.n_tiles) * hp.n_tiles);
+      const uint32_t budget = 227u * 1024;
+      const uint32_t b_bytes = uint32_t(pl->block_n) * 128;
+      const uint32_t slab = 9u * uint32_t(hp.cblks) * b_bytes;
+      const uint32_t out_bytes = uint32_t(pl->block_n / 64) * kChunkBytes;
+      hp.b_stationary = (slab <= 80u * 1024 && hp.total_tiles >= 2 * grid) ? 1 : 0;
+      hp.b_stages = hp.b_stationary ? 1 : 4;
+      const uint32_t fixed = 1024u + (hp.b_stationary ? slab : uint32_t(hp.b_stages) * b_bytes) + 2 * out_bytes +
+                             uint32_t(pl->block_n) * 4 + 8u * (2 * 8 + 2 * 4 + 4) + 64;
+      hp.halo_stages = std::max(2, std::min(8, int((budget - fixed) / kHaloStageBytes)));
+      pl->smem_bytes = fixed + uint32_t(hp.halo_stages) * kHaloStageBytes;
+      pl->grid = grid;
+      std::string hmsg;
+      uint64_t dims[4] = {uint64_t(g.Cin), uint64_t(g.W), uint64_t(g.H), uint64_t(g.B)};
+      uint64_t str[3] = {uint64_t(g.Cin) * 2, uint64_t(g.W) * g.Cin * 2, uint64_t(g.H) * g.W * g.Cin * 2};
+      uint32_t box[4] = {64, uint32_t(kHaloPW), uint32_t(kHaloPH), 1};
+      uint32_t es[4] = {1, 1, 1, 1};
+      bool hok = encode(&pl->tmA, dt, 4, in, dims, str, box, es, false, hmsg);
+      if (hok) {
+        const uint64_t K = 9ull * g.Cin;
+        uint64_t wd[2] = {K, uint64_t(g.Cout)};
+        uint64_t ws[1] = {K * 2};
+        uint32_t wb[2] = {64, uint32_t(pl->block_n)};
+        uint32_t we[2] = {1, 1};
+        hok = encode(&pl->tmW, dt, 2, w_packed, wd, ws, wb, we, false, hmsg);
+      }
+      if (hok) {
+        uint64_t od[4] = {uint64_t(g.Cout), uint64_t(g.Wo), uint64_t(g.Ho), uint64_t(g.B)};
+        uint64_t os[3] = {uint64_t(g.Cout) * 2, uint64_t(g.Wo) * g.Cout * 2, uint64_t(g.Ho) * g.Wo * g.Cout * 2};
+        uint32_t ob[4] = {64, uint32_t(kHaloBW), uint32_t(kHaloBH), 1};
+        hok = encode(&pl->tmOut, dt, 4, e.out, od, os, ob, es, false, hmsg);
+      }
+      if (!hok) { delete pl; return failmsg(hmsg); }
+      pl->tmAct = pl->tmOut; pl->tmRes = pl->tmOut;
+      return pl;
+    }
+  }
   plan_geometry(*pl);
   const int bw = p.bw, bh = p.bh, bn = p.bn;
 

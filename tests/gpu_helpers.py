@@ -129,5 +129,8 @@ CONV_CASES = [
     ("1x1 256->64 @56 prologue", dict(B=2, H=56, W=56, Cin=256, Cout=64, k=1, stride=1, pad=0, relu=1, prologue=True)),
     ("1x1 s2 512->1024 @28 prologue", dict(B=3, H=28, W=28, Cin=512, Cout=1024, k=1, stride=2, pad=0, prologue=True)),
     ("1x1 1024->256 @14 prologue B40", dict(B=40, H=14, W=14, Cin=1024, Cout=256, k=1, stride=1, pad=0, relu=1, prologue=True)),
+    ("3x3 s1 64->128 @30x17 B3 (halo, ragged)", dict(B=3, H=30, W=17, Cin=64, Cout=128, k=3, stride=1, pad=1)),
+    ("3x3 s1 128->64 @14 B7 (halo)", dict(B=7, H=14, W=14, Cin=128, Cout=64, k=3, stride=1, pad=1, relu=1)),
+    ("3x3 s1 64->64 @56 B9 (halo, many tiles)", dict(B=9, H=56, W=56, Cin=64, Cout=64, k=3, stride=1, pad=1, relu=1)),
     ("3x3 s1 256->256 @14 B64 (N=256 tiles)", dict(B=64, H=14, W=14, Cin=256, Cout=256, k=3, stride=1, pad=1, relu=1)),
 ]
