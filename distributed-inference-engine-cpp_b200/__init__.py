@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200rn.so")
+LIB_PATH = os.environ.get("B200RN_LIB") or os.path.join(_HERE, "libb200rn.so")   # B200RN_LIB: A/B another build
 
 MODE_EXACT, MODE_BF16, MODE_FP16 = 0, 1, 2
 MODES = {"exact": MODE_EXACT, "fp32": MODE_EXACT, "bf16": MODE_BF16, "fp16": MODE_FP16}

@@ -46,7 +46,9 @@ struct UmmaParams {
   int relaxed_store_wait;   // staging is double-buffered: the previous tile's TMA stores may still be reading
   int has_res, has_out, has_act, relu, act_relu;
   int has_pre, pre_relu, cin;
-  int dbg_ashift, dbg_baseoff;   // descriptor experiment (B200RN_DBG_ASHIFT / B200RN_DBG_BASEOFF), 0 in production
+  int dbg_ashift;   // descriptor experiment (B200RN_DBG_ASHIFT, tools/dbg_ashift.py), 0 in production
+  unsigned long long* trace;   // timeline experiment (B200RN_DBG_TRACE): CTA 0 stamps clock64 per tile and actor
+  int kgroup;         // K blocks per pipeline stage / barrier (fewer waits and commits for the MMA thread)
   int b_stationary;   // the CTA's whole weight slab (all K blocks of its N tile) is loaded once and stays in smem
   uint32_t a_bytes, b_bytes, rows;
   const float* bias;
@@ -138,6 +140,27 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t da, uint64_t 
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
       "}" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
+// Same instruction, descriptors given as their low words (start address >> 4 | LBO); the high word (SBO,
+// version, swizzle mode) is the same for A and B.  The single issuing thread is latency-bound on its own
+// instruction stream, so descriptor arithmetic is kept to one 32-bit add per operand.
+__device__ __forceinline__ void umma_f16_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %5, 0;\n\t"
+      "mov.b64 da, {%1, %3};\n\t"
+      "mov.b64 db, {%2, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t"
+      "}" ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
+template <int KB>
+__device__ __forceinline__ constexpr uint32_t smem_desc_hi() {
+  return ((8u * KB) >> 4) | (1u << 14) | ((KB == 128 ? 2u : 4u) << 29);
+}
+__device__ __forceinline__ uint32_t smem_desc_lo(uint32_t smem_addr) { return ((smem_addr & 0x3FFFF) >> 4) | (1u << 16); }
+
 __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -244,8 +267,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr int kMmaPerBlock = KB / 32;        // UMMA_K = 16 elements = 32 bytes
   constexpr uint32_t A_BYTES = kTileM * KB;
   constexpr uint32_t B_BYTES = BLOCK_N * KB;
-  // a pipeline stage holds an A tile and, unless the weights are stationary, the matching B tile
-  const uint32_t STAGE_BYTES = p.b_stationary ? A_BYTES : A_BYTES + B_BYTES;
+  // a pipeline stage holds kgroup K blocks: each an A tile and, unless the weights are stationary, its B tile
+  const uint32_t SLOT_BYTES = p.b_stationary ? A_BYTES : A_BYTES + B_BYTES;
+  const uint32_t STAGE_BYTES = uint32_t(p.kgroup) * SLOT_BYTES;
   constexpr uint32_t RAW_BYTES = kChunks * kChunkBytes;   // one tile's raw / residual staging
 
   extern __shared__ uint8_t smem_raw[];
@@ -326,19 +350,23 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++i) {
         const TileCoord tc = decode_tile(p, tile, BLOCK_N);
-        for (int it = 0; it < p.num_k_iters; ++it) {
+        for (int it0 = 0; it0 < p.num_k_iters; it0 += p.kgroup) {
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
+          if (p.trace && blockIdx.x == 0 && i < 64 && it0 == 0) p.trace[i * 8 + 0] = clock64();
           const uint32_t fb = smem_u32(&full_bar[stage]);
-          const uint32_t a_dst = smem_u32(pipe + stage * STAGE_BYTES);
-          mbar_expect_tx(fb, p.b_stationary ? p.a_bytes : p.a_bytes + p.b_bytes);
-          if (p.stem) {
-            tma_load_5d(a_dst, &tmA, fb, 0, tc.w0, it & 1, tc.h0 + (it >> 1), tc.n0);
-          } else {
-            const int tap = it / p.cblks, cb = it - tap * p.cblks;
-            const int ky = tap / p.kw, kx = tap - ky * p.kw;
-            tma_load_4d(a_dst, &tmA, fb, cb * 64, tc.w0 * p.stride - p.pad + kx, tc.h0 * p.stride - p.pad + ky, tc.n0);
+          mbar_expect_tx(fb, uint32_t(p.kgroup) * (p.b_stationary ? p.a_bytes : p.a_bytes + p.b_bytes));
+          for (int j = 0; j < p.kgroup; ++j) {
+            const int it = it0 + j;
+            const uint32_t a_dst = smem_u32(pipe + stage * STAGE_BYTES + j * SLOT_BYTES);
+            if (p.stem) {
+              tma_load_5d(a_dst, &tmA, fb, 0, tc.w0, it & 1, tc.h0 + (it >> 1), tc.n0);
+            } else {
+              const int tap = it / p.cblks, cb = it - tap * p.cblks;
+              const int ky = tap / p.kw, kx = tap - ky * p.kw;
+              tma_load_4d(a_dst, &tmA, fb, cb * 64, tc.w0 * p.stride - p.pad + kx, tc.h0 * p.stride - p.pad + ky, tc.n0);
+            }
+            if (!p.b_stationary) tma_load_2d(a_dst + A_BYTES, &tmW, fb, it * (KB / 2), tc.col0);
           }
-          if (!p.b_stationary) tma_load_2d(a_dst + A_BYTES, &tmW, fb, it * (KB / 2), tc.col0);
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
         if (p.has_res) {
@@ -357,32 +385,41 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1) {
     // ===== MMA issuer: one elected thread runs the whole loop (waits, tcgen05.mma, commits) =====
     constexpr uint32_t idesc = make_idesc<T, BLOCK_N>();
+    constexpr uint32_t desc_hi = smem_desc_hi<KB>();
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       int i = 0;
+      const uint32_t pipe_lo = smem_desc_lo(smem_u32(pipe));
+      const uint32_t bstat_lo = smem_desc_lo(smem_u32(bstat));
+      const uint32_t dbg_off = uint32_t(p.dbg_ashift) * 8;   // descriptor experiment only (tools/dbg_ashift.py)
       if (p.b_stationary && int(blockIdx.x) < p.total_tiles) mbar_wait(smem_u32(bstat_bar), 0);
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++i) {
         const int buf = i & 1;
+        const bool tr = p.trace && blockIdx.x == 0 && i < 64;
+        if (tr) p.trace[i * 8 + 1] = clock64();
         mbar_wait(smem_u32(&tmem_empty[buf]), ((i >> 1) & 1) ^ 1);   // epilogue drained this accumulator
         tc_fence_after();
+        if (tr) p.trace[i * 8 + 2] = clock64();
         const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
-        for (int it = 0; it < p.num_k_iters; ++it) {
+        for (int it0 = 0; it0 < p.num_k_iters; it0 += p.kgroup) {
           mbar_wait(smem_u32(p.has_pre ? &xf_bar[stage] : &full_bar[stage]), phase);
           tc_fence_after();
-          const uint32_t a_addr = smem_u32(pipe + stage * STAGE_BYTES);
-          const uint32_t b_addr = p.b_stationary ? smem_u32(bstat + it * B_BYTES) : a_addr + A_BYTES;
+          if (tr && it0 == 0) p.trace[i * 8 + 3] = clock64();
+          const uint32_t st_lo = pipe_lo + uint32_t(stage) * (STAGE_BYTES >> 4) + dbg_off;
+          for (int j = 0; j < p.kgroup; ++j) {
+            const int it = it0 + j;
+            const uint32_t a_lo = st_lo + uint32_t(j) * (SLOT_BYTES >> 4);
+            const uint32_t b_lo = p.b_stationary ? bstat_lo + uint32_t(it) * (B_BYTES >> 4) : a_lo + (A_BYTES >> 4);
 #pragma unroll
-          for (int k = 0; k < kMmaPerBlock; ++k) {
-            uint64_t da = make_smem_desc<KB>(a_addr + k * 32 + p.dbg_ashift * 128);
-            if (p.dbg_baseoff) da |= uint64_t(((a_addr + p.dbg_ashift * 128) >> 7) & 7) << 49;
-            const uint64_t db = make_smem_desc<KB>(b_addr + k * 32);
-            umma_f16(tmem_d, da, db, idesc, (it | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < kMmaPerBlock; ++k)
+              umma_f16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (it | k) != 0 ? 1u : 0u);
           }
-          umma_commit(smem_u32(&empty_bar[stage]));                               // frees the smem slot
-          if (it == p.num_k_iters - 1) umma_commit(smem_u32(&tmem_full[buf]));     // accumulator complete
+          umma_commit(smem_u32(&empty_bar[stage]));                                             // frees the smem slot
+          if (it0 + p.kgroup >= p.num_k_iters) umma_commit(smem_u32(&tmem_full[buf]));           // accumulator complete
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
+        if (tr) p.trace[i * 8 + 4] = clock64();
       }
     }
   } else if (warp >= 2 + kEpiWarps) {
@@ -457,9 +494,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         else tma_store_wait_read();
         if (f_res) mbar_arrive(smem_u32(&res_empty[(p.raw_bufs == 2) ? ((i - 1) & 1) : 0]));
       }
+      const bool etr = p.trace && blockIdx.x == 0 && store_thread && i < 64;
+      if (etr) p.trace[i * 8 + 5] = clock64();
       asm volatile("bar.sync 1, 256;" ::: "memory");
       mbar_wait(smem_u32(&tmem_full[buf]), par);
       tc_fence_after();
+      if (etr) p.trace[i * 8 + 6] = clock64();
       const int rb = (p.raw_bufs == 2) ? (i & 1) : 0;
       if (f_res) mbar_wait(smem_u32(&res_full[rb]), (p.raw_bufs == 2) ? par : uint32_t(i & 1));
       uint8_t* raw_tile = rawbuf + rb * RAW_BYTES;
@@ -523,6 +563,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           tma_store_commit();
         }
       }
+      if (etr) p.trace[i * 8 + 7] = clock64();
     }
     if (store_thread) tma_store_wait_read();
   }
@@ -549,6 +590,8 @@ constexpr uint32_t kHaloStageBytes = 21 * 1024;                   // + junk rows
 struct HaloParams {
   int cblks, n_tiles, total_tiles, tiles_w, tiles_h;
   int halo_stages, b_stages, b_stationary, relu;
+  unsigned long long* trace;   // timeline experiment (B200RN_DBG_TRACE): CTA 0 stamps clock64 per tile and actor
+  int dbg_skip;   // bottleneck experiment (B200RN_DBG_SKIP): 1 = issue no MMA, 2 = no epilogue math/stores, 4 = one MMA per tap
   const float* bias;
 };
 
@@ -623,6 +666,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_con
         const uint32_t fb = smem_u32(&halo_full[slot]);
         mbar_expect_tx(fb, kHaloLoadBytes);
         tma_load_4d(smem_u32(halo + slot * kHaloStageBytes), &tmHalo, fb, cb * 64, x0 - 1, y0 - 1, n);
+        if (p.trace && blockIdx.x == 0 && hq < 64) p.trace[hq * 8 + 0] = clock64();
       };
       int hq = 0, bstage = 0;
       uint32_t bphase = 0;
@@ -654,46 +698,55 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_con
   } else if (warp == 1) {
     // ===== MMA issuer: one elected thread =====
     constexpr uint32_t idesc = make_idesc<T, BLOCK_N>();
+    constexpr uint32_t desc_hi = smem_desc_hi<128>();
     if (elect_one()) {
+      const uint32_t halo_lo = smem_desc_lo(smem_u32(halo));
+      const uint32_t bbuf_lo = smem_desc_lo(smem_u32(bbuf));
       if (p.b_stationary && my_tiles > 0) mbar_wait(smem_u32(&b_full[0]), 0);
       int q = 0, bstage = 0;
       uint32_t bphase = 0;
       for (int i = 0; i < my_tiles; ++i) {
         const int buf = i & 1;
+        if (p.trace && blockIdx.x == 0 && i < 64) p.trace[i * 8 + 6] = clock64();
         mbar_wait(smem_u32(&tmem_empty[buf]), ((i >> 1) & 1) ^ 1);
         tc_fence_after();
+        if (p.trace && blockIdx.x == 0 && i < 64) p.trace[i * 8 + 7] = clock64();
         const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
         for (int cb = 0; cb < p.cblks; ++cb, ++q) {
           const int slot = q % HS;
+          if (p.trace && blockIdx.x == 0 && q < 64) p.trace[q * 8 + 1] = clock64();
           mbar_wait(smem_u32(&halo_full[slot]), uint32_t(q / HS) & 1);
           tc_fence_after();
-          const uint32_t a_base = smem_u32(halo + slot * kHaloStageBytes);
-#pragma unroll 1
-          for (int ky = 0; ky < 3; ++ky) {
+          if (p.trace && blockIdx.x == 0 && q < 64) p.trace[q * 8 + 2] = clock64();
+          const uint32_t a_lo = halo_lo + uint32_t(slot) * (kHaloStageBytes >> 4);
 #pragma unroll
-            for (int kx = 0; kx < 3; ++kx) {
-              const int tap = ky * 3 + kx;
-              uint32_t b_addr;
-              if (p.b_stationary) {
-                b_addr = smem_u32(bbuf + (tap * p.cblks + cb) * B_BYTES);
-              } else {
-                mbar_wait(smem_u32(&b_full[bstage]), bphase);
-                tc_fence_after();
-                b_addr = smem_u32(bbuf + bstage * B_BYTES);
-              }
-              const uint32_t a_addr = a_base + uint32_t(ky * kHaloPW + kx) * 128;   // row-shifted view of the patch
+          for (int tap = 0; tap < 9; ++tap) {
+            uint32_t b_lo;
+            if (p.b_stationary) {
+              b_lo = bbuf_lo + uint32_t(tap * p.cblks + cb) * (B_BYTES >> 4);
+            } else {
+              mbar_wait(smem_u32(&b_full[bstage]), bphase);
+              tc_fence_after();
+              b_lo = bbuf_lo + uint32_t(bstage) * (B_BYTES >> 4);
+            }
+            // row-shifted view of the patch: tap (ky,kx) starts ky*16 + kx rows (of 128 bytes) further on
+            const uint32_t a_tap = a_lo + uint32_t((tap / 3) * kHaloPW + (tap % 3)) * 8;
+            if (!(p.dbg_skip & 1)) {
 #pragma unroll
               for (int k = 0; k < 4; ++k)
-                umma_f16(tmem_d, make_smem_desc<128>(a_addr + k * 32), make_smem_desc<128>(b_addr + k * 32), idesc,
-                         (cb | tap | k) != 0 ? 1u : 0u);
-              if (!p.b_stationary) {
-                umma_commit(smem_u32(&b_empty[bstage]));
-                if (++bstage == SB) { bstage = 0; bphase ^= 1; }
-              }
+                if (k == 0 || !(p.dbg_skip & 4))
+                  umma_f16_lo(tmem_d, a_tap + 2 * k, b_lo + 2 * k, desc_hi, idesc, (tap | k) != 0 ? 1u : uint32_t(cb != 0));
+            }
+            if (!p.b_stationary) {
+              umma_commit(smem_u32(&b_empty[bstage]));
+              if (++bstage == SB) { bstage = 0; bphase ^= 1; }
             }
           }
+          if (p.trace && blockIdx.x == 0 && q < 64) p.trace[q * 8 + 3] = clock64();
           umma_commit(smem_u32(&halo_empty[slot]));
+          if (p.trace && blockIdx.x == 0 && q < 64) p.trace[q * 8 + 4] = clock64();
           if (cb == p.cblks - 1) umma_commit(smem_u32(&tmem_full[buf]));
+          if (p.trace && blockIdx.x == 0 && q < 64) p.trace[q * 8 + 5] = clock64();
         }
       }
     }
@@ -717,10 +770,14 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_con
         cur_ntile = tile % p.n_tiles;
         for (int k = et; k < BLOCK_N; k += kEpiThreads) s_bias[k] = __ldg(p.bias + col0 + k);
       }
+      const bool tr = false;
+      if (tr) p.trace[i * 8 + 4] = clock64();
       if (store_thread && i > 0) tma_store_wait_read_pending<kChunks>();   // tile i-2's staging is free again
       asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (tr) p.trace[i * 8 + 5] = clock64();
       mbar_wait(smem_u32(&tmem_full[buf]), (i >> 1) & 1);
       tc_fence_after();
+      if (tr) p.trace[i * 8 + 6] = clock64();
       uint8_t* out_tile = outbuf + buf * OUT_BYTES;
 #pragma unroll 1
       for (int c = 0; c < kChunks; ++c) {
@@ -733,7 +790,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_con
         }
         uint8_t* stage = out_tile + c * kChunkBytes;
         uint4* out_row = reinterpret_cast<uint4*>(stage + drow * 128);
-        if (valid) {
+        if (valid && !(p.dbg_skip & 2)) {
 #pragma unroll
           for (int jj = 0; jj < 4; ++jj) {
             const int j = g * 4 + jj;
@@ -754,10 +811,193 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_con
         }
         fence_proxy_async_smem();
         asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (store_thread) {
+        if (store_thread && !(p.dbg_skip & 2)) {
           tma_store_4d(&tmOutRow, smem_u32(stage), col0 + c * 64, x0, y0, n);   // box {64 ch, 14, 8, 1}
           tma_store_commit();
         }
+      }
+      if (tr) p.trace[i * 8 + 7] = clock64();
+    }
+    if (store_thread) tma_store_wait_read();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
+}
+
+// ---- 7x7 / stride 2 / pad 3 stem, one input patch per tile ------------------------------------------
+// The generic kernel fetches the stem's A operand as 7 boxes of 128 rows x 64 bytes per tile; the TMA unit
+// needs ~4 cycles per such row, which made the stem the slowest layer of the network (measured timeline:
+// 3850 cycles per tile, all of it waiting for those 896 rows).  Here a tile is 8 x 16 output pixels
+// (M row r = y*8 + x) and the zero-framed fp16 input patch it needs -- 37 rows of 22 pixels x 4 channels =
+// 176 bytes -- is fetched ONCE (37 TMA rows).  Both operands use the un-swizzled K-major layout, whose
+// "core matrix" is 8 rows x 16 bytes at a 16-byte row pitch: for the A operand of filter row ky the 8 rows
+// of a core matrix are 8 consecutive output pixels (input pixels 2x apart = 16 bytes apart), the next 16-byte
+// K chunk lies 16 bytes further (LBO = 16: the chunks of neighbouring pixels overlap, which is exactly the
+// sliding window), and the next output row is two patch rows down (SBO = 352).  No im2col copy exists even
+// in shared memory.  K per filter row = 8 pixels x 4 channels = 32 (two K=16 MMAs); the 8th pixel and the 4th
+// channel carry zero weights.  Weights (28 KB per 64 output channels) are loaded once per CTA by a bulk copy.
+constexpr int kStemTW = 8, kStemTH = 16;                       // output tile
+constexpr int kStemPatchRows = 2 * kStemTH + 5;                // 37
+constexpr int kStemPatchPx = 2 * kStemTW + 6;                  // 22
+constexpr uint32_t kStemPatchPitch = kStemPatchPx * 8;         // 176 bytes
+constexpr uint32_t kStemPatchBytes = kStemPatchRows * kStemPatchPitch;   // 6512
+constexpr uint32_t kStemStageBytes = 6656;                     // 128-byte multiple
+constexpr uint32_t kStemWBytes = 7 * 4096;                     // one 64-channel N tile of packed weights
+
+struct Stem2Params {
+  int tiles_w, tiles_h, n_tiles, total_tiles, stages, relu;
+  const float* bias;
+  const void* w_packed;
+};
+
+// un-swizzled K-major descriptor: start | LBO (K-adjacent core matrices) | SBO (8-row groups) | version 1
+__device__ __forceinline__ uint64_t make_desc_noswz(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return uint64_t((addr & 0x3FFFF) >> 4) | (uint64_t(lbo_bytes >> 4) << 16) | (uint64_t(sbo_bytes >> 4) << 32) | (uint64_t(1) << 46);
+}
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+               ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kBaseThreads, 1)
+stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constant__ CUtensorMap tmOut, const Stem2Params p) {
+  constexpr int BLOCK_N = 64;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int S = p.stages;
+  uint8_t* wbuf = smem;                                   // 28 KB, stationary
+  uint8_t* outbuf = wbuf + kStemWBytes;                   // 2 x 16 KB staging (SWIZZLE_128B rows)
+  uint8_t* patch = outbuf + 2 * kChunkBytes;              // S x kStemStageBytes
+  float* s_bias = reinterpret_cast<float*>(patch + S * kStemStageBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_bias + BLOCK_N);
+  uint64_t* full_bar = bars;            // [S]
+  uint64_t* empty_bar = bars + S;       // [S]
+  uint64_t* w_bar = empty_bar + S;      // [1]
+  uint64_t* tmem_full = w_bar + 1;      // [2]
+  uint64_t* tmem_empty = tmem_full + 2; // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int my_tiles = (int(blockIdx.x) < p.total_tiles) ? (p.total_tiles - 1 - int(blockIdx.x)) / int(gridDim.x) + 1 : 0;
+  const int n_tile = int(blockIdx.x) % p.n_tiles;         // gridDim.x is a multiple of n_tiles
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmPatch);
+    prefetch_tmap(&tmOut);
+    for (int i = 0; i < S; ++i) { mbar_init(smem_u32(&full_bar[i]), 1); mbar_init(smem_u32(&empty_bar[i]), 1); }
+    mbar_init(smem_u32(w_bar), 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&tmem_full[i]), 1); mbar_init(smem_u32(&tmem_empty[i]), kEpiThreads); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * BLOCK_N);
+  if (warp >= 2)
+    for (int k = threadIdx.x - 64; k < BLOCK_N; k += kEpiThreads) s_bias[k] = __ldg(p.bias + n_tile * BLOCK_N + k);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  auto tile_coord = [&](int i, int& x0, int& y0, int& n) {
+    int mt = (int(blockIdx.x) + i * int(gridDim.x)) / p.n_tiles;
+    const int tw = mt % p.tiles_w; mt /= p.tiles_w;
+    const int th = mt % p.tiles_h;
+    n = mt / p.tiles_h;
+    x0 = tw * kStemTW; y0 = th * kStemTH;
+  };
+
+  if (warp == 0) {
+    if (elect_one() && my_tiles > 0) {
+      mbar_expect_tx(smem_u32(w_bar), kStemWBytes);
+      bulk_load_1d(smem_u32(wbuf), static_cast<const uint8_t*>(p.w_packed) + size_t(n_tile) * kStemWBytes, kStemWBytes, smem_u32(w_bar));
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < my_tiles; ++i) {
+        int x0, y0, n;
+        tile_coord(i, x0, y0, n);
+        mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
+        const uint32_t fb = smem_u32(&full_bar[stage]);
+        mbar_expect_tx(fb, kStemPatchBytes);
+        // frame coordinates: pixel (2*x0, 2*y0) of the zero-framed input = tap (0,0) of output (x0, y0)
+        tma_load_3d(smem_u32(patch + stage * kStemStageBytes), &tmPatch, fb, 2 * x0 * 4, 2 * y0, n);
+        if (++stage == S) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc<T, BLOCK_N>();
+    if (elect_one() && my_tiles > 0) {
+      mbar_wait(smem_u32(w_bar), 0);
+      const uint32_t w_addr = smem_u32(wbuf);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < my_tiles; ++i) {
+        const int buf = i & 1;
+        mbar_wait(smem_u32(&tmem_empty[buf]), ((i >> 1) & 1) ^ 1);
+        mbar_wait(smem_u32(&full_bar[stage]), phase);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
+        const uint32_t a_addr = smem_u32(patch + stage * kStemStageBytes);
+#pragma unroll
+        for (int ky = 0; ky < 7; ++ky)
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            const uint64_t da = make_desc_noswz(a_addr + ky * kStemPatchPitch + m * 32, 16, 2 * kStemPatchPitch);
+            const uint64_t db = make_desc_noswz(w_addr + ky * 4096 + m * 256, 128, 512);
+            umma_f16(tmem_d, da, db, idesc, (ky | m) != 0 ? 1u : 0u);
+          }
+        umma_commit(smem_u32(&empty_bar[stage]));
+        umma_commit(smem_u32(&tmem_full[buf]));
+        if (++stage == S) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    const int q4 = warp & 3;
+    const int g = (warp - 2) >> 2;
+    const int row = q4 * 32 + lane;            // = y*8 + x, the order the {64, 8, 16, 1} store box expects
+    const int sw = row & 7;
+    const bool store_thread = (warp == 2 && lane == 0);
+    for (int i = 0; i < my_tiles; ++i) {
+      int x0, y0, n;
+      tile_coord(i, x0, y0, n);
+      const int buf = i & 1;
+      if (store_thread && i > 0) tma_store_wait_read_pending<1>();   // tile i-2's staging buffer is free again
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      mbar_wait(smem_u32(&tmem_full[buf]), (i >> 1) & 1);
+      tc_fence_after();
+      uint32_t acc[32];
+      tmem_ld_32x32b_x32(tmem_base + (uint32_t(q4 * 32) << 16) + uint32_t(buf * BLOCK_N + g * 32), acc);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(smem_u32(&tmem_empty[buf]));
+      uint8_t* stage_out = outbuf + buf * kChunkBytes;
+      uint4* out_row = reinterpret_cast<uint4*>(stage_out + row * 128);
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+        const int j = g * 4 + jj;
+        const float4 b0 = *reinterpret_cast<const float4*>(s_bias + j * 8);
+        const float4 b1 = *reinterpret_cast<const float4*>(s_bias + j * 8 + 4);
+        float v[8];
+        v[0] = __uint_as_float(acc[jj * 8 + 0]) + b0.x; v[1] = __uint_as_float(acc[jj * 8 + 1]) + b0.y;
+        v[2] = __uint_as_float(acc[jj * 8 + 2]) + b0.z; v[3] = __uint_as_float(acc[jj * 8 + 3]) + b0.w;
+        v[4] = __uint_as_float(acc[jj * 8 + 4]) + b1.x; v[5] = __uint_as_float(acc[jj * 8 + 5]) + b1.y;
+        v[6] = __uint_as_float(acc[jj * 8 + 6]) + b1.z; v[7] = __uint_as_float(acc[jj * 8 + 7]) + b1.w;
+        if (p.relu) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+        }
+        out_row[j ^ sw] = make_uint4(pack2<T>(v[0], v[1]), pack2<T>(v[2], v[3]), pack2<T>(v[4], v[5]), pack2<T>(v[6], v[7]));
+      }
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (store_thread) {
+        tma_store_4d(&tmOut, smem_u32(stage_out), n_tile * BLOCK_N, x0, y0, n);   // box {64 ch, 8, 16, 1}
+        tma_store_commit();
       }
     }
     if (store_thread) tma_store_wait_read();
@@ -786,8 +1026,9 @@ EncodeTiledFn encode_fn() {
   return fn;
 }
 
+// swz: 0 = SWIZZLE_128B, 1 = SWIZZLE_64B, 2 = none
 bool encode(CUtensorMap* m, DType dt, int rank, const void* base, const uint64_t* dims, const uint64_t* strides_bytes,
-            const uint32_t* box, const uint32_t* estr, bool sw64, std::string& err) {
+            const uint32_t* box, const uint32_t* estr, int swz, std::string& err) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) { err = "cuTensorMapEncodeTiled is not available from the driver"; return false; }
   cuuint64_t d[5]; cuuint64_t s[4]; cuuint32_t b[5], e[5];
@@ -795,8 +1036,8 @@ bool encode(CUtensorMap* m, DType dt, int rank, const void* base, const uint64_t
   for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
   CUresult r = fn(m, dt == DType::BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
                   cuuint32_t(rank), const_cast<void*>(base), d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  sw64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  swz == 1 ? CU_TENSOR_MAP_SWIZZLE_64B : (swz == 2 ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B),
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     char buf[256];
     std::snprintf(buf, sizeof buf, "cuTensorMapEncodeTiled failed (CUresult %d) rank=%d dims=[%llu,%llu,%llu,%llu] box=[%u,%u,%u,%u]",
@@ -836,6 +1077,8 @@ struct UmmaConvPlan {
   int grid;
   int halo = 0;           // 3x3/s1/p1 layer routed to conv3x3_halo_kernel (tmA = patch map, tmOut = row-store map)
   HaloParams hp;
+  int stem2 = 0;          // stem routed to stem7x7_kernel (tmA = patch map, tmOut = {64, 8, 16, 1} store map)
+  Stem2Params sp;
 };
 
 bool umma_conv_supported(const ConvGeom& g, int stem_mode, char* why, size_t cap) {
@@ -865,6 +1108,21 @@ static void pack_weights_t(const float* w, const ConvGeom& g, int stem_mode, T* 
   if (!stem_mode) {
     size_t n = size_t(g.Cout) * g.kh * g.kw * g.Cin;   // already [Cout][ky][kx][Cin] = K-major
     for (size_t i = 0; i < n; ++i) dst[i] = host_cvt<T>(w[i]);
+    return;
+  }
+  if (stem_mode == 2) {
+    // stem7x7_kernel: per 64-channel N tile, per filter row ky a 4 KB block of un-swizzled K-major core matrices
+    // [n_group 0..7][k_core 0..3][8 rows x 16 bytes]; k = kx*4 + c (kx = 7 and c = 3 are zero)
+    std::memset(dst, 0, size_t(g.Cout) * 7 * 32 * sizeof(T));
+    for (int o = 0; o < g.Cout; ++o)
+      for (int ky = 0; ky < 7; ++ky)
+        for (int kx = 0; kx < 7; ++kx)
+          for (int c = 0; c < 4; ++c) {
+            const int k = kx * 4 + c;
+            const size_t byte = size_t(o / 64) * (7 * 4096) + size_t(ky) * 4096 + size_t((o % 64) / 8) * 512 + size_t(k / 8) * 128 +
+                                size_t(o % 8) * 16 + size_t(k % 8) * 2;
+            dst[byte / 2] = host_cvt<T>(w[((size_t(o) * 7 + ky) * 7 + kx) * g.Cin + c]);
+          }
     return;
   }
   // stem: [Cout][ky 0..6][kx 0..7][c 0..3]; kx = 7 is zero (8-pixel granule), c = 3 is the pad channel
@@ -984,6 +1242,16 @@ static void plan_geometry(UmmaConvPlan& pl) {
     stage_eff = a_only;
     pl.grid = grid_bs;
   }
+  // K blocks per stage: the largest divisor of the K-block count that keeps a stage <= 64 KB and >= 3 stages
+  p.kgroup = 1;
+  const char* kg_env = std::getenv("B200RN_KGROUP");
+  if (!p.has_pre && !(kg_env && kg_env[0] == '0'))
+    for (int kg = std::min(8, p.num_k_iters); kg > 1; --kg)
+      if (p.num_k_iters % kg == 0 && uint32_t(kg) * stage_eff <= 64u * 1024 && (budget - fixed) / (uint32_t(kg) * stage_eff) >= 3) {
+        p.kgroup = kg;
+        break;
+      }
+  stage_eff *= uint32_t(p.kgroup);
   int stages = int((budget - fixed) / stage_eff);
   stages = std::max(2, std::min(stages, 8));
   p.num_stages = stages;
@@ -1036,8 +1304,24 @@ static cudaError_t launch_halo(const UmmaConvPlan* pl, cudaStream_t s) {
   return cudaGetLastError();
 }
 
+template <typename T>
+static cudaError_t launch_stem2(const UmmaConvPlan* pl, cudaStream_t s) {
+  auto kern = stem7x7_kernel<T>;
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    configured_device = dev;
+  }
+  kern<<<pl->grid, kBaseThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmOut, pl->sp);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
   const bool bf = pl->dt == DType::BF16;
+  if (pl->stem2) return bf ? launch_stem2<__nv_bfloat16>(pl, s) : launch_stem2<__half>(pl, s);
   if (pl->halo) {
     if (pl->block_n == 64) return bf ? launch_halo<__nv_bfloat16, 64>(pl, s) : launch_halo<__half, 64>(pl, s);
     return bf ? launch_halo<__nv_bfloat16, 128>(pl, s) : launch_halo<__half, 128>(pl, s);
@@ -1065,11 +1349,51 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   p.relu = e.relu; p.act_relu = e.act_relu;
   p.bias = e.bias; p.act_scale = e.act_scale; p.act_shift = e.act_shift;
   p.has_pre = e.pre_scale != nullptr; p.pre_relu = e.pre_relu; p.cin = g.Cin;
+  if (std::getenv("B200RN_DBG_TRACE")) {
+    cudaMalloc(&p.trace, 64 * 8 * sizeof(unsigned long long));
+    cudaMemset(p.trace, 0, 64 * 8 * sizeof(unsigned long long));
+  }
   if (const char* v = std::getenv("B200RN_DBG_ASHIFT")) p.dbg_ashift = std::atoi(v);
-  if (const char* v = std::getenv("B200RN_DBG_BASEOFF")) p.dbg_baseoff = std::atoi(v);
   p.pre_scale = e.pre_scale; p.pre_shift = e.pre_shift;
   if (p.has_pre && (stem_mode || g.kh != 1 || g.kw != 1 || g.pad != 0)) { delete pl; return failmsg("operand prologue needs a 1x1, pad-0 conv"); }
   if (!p.has_out && !p.has_act) { delete pl; return failmsg("conv with no output"); }
+  if (stem_mode == 2) {
+    if (!p.has_out || p.has_res || p.has_act || p.has_pre) { delete pl; return failmsg("stem kernel supports bias + ReLU + one output only"); }
+    Stem2Params& sp = pl->sp;
+    std::memset(&sp, 0, sizeof sp);
+    pl->stem2 = 1;
+    pl->kb = 64; pl->block_n = 64;
+    sp.tiles_w = (g.Wo + kStemTW - 1) / kStemTW;
+    sp.tiles_h = (g.Ho + kStemTH - 1) / kStemTH;
+    sp.n_tiles = g.Cout / 64;
+    sp.total_tiles = sp.tiles_w * sp.tiles_h * g.B * sp.n_tiles;
+    sp.relu = e.relu;
+    sp.bias = e.bias;
+    sp.w_packed = w_packed;
+    const int sms = sm_count();
+    int grid = std::min(sp.total_tiles, sms);
+    grid = std::max(sp.n_tiles, (grid / sp.n_tiles) * sp.n_tiles);
+    const uint32_t fixed = 1024u + kStemWBytes + 2u * kChunkBytes + 64u * 4 + 8u * (2 * 16 + 5) + 64;
+    sp.stages = std::max(2, std::min(16, int((227u * 1024 - fixed) / kStemStageBytes)));
+    pl->smem_bytes = fixed + uint32_t(sp.stages) * kStemStageBytes;
+    pl->grid = grid;
+    std::string smsg;
+    const int Hp = stem_Hp(g.H), Wp = stem_Wp(g.W);
+    uint64_t dims[3] = {uint64_t(Wp) * 4, uint64_t(Hp), uint64_t(g.B)};
+    uint64_t str[2] = {uint64_t(Wp) * 8, uint64_t(Hp) * Wp * 8};
+    uint32_t box[3] = {uint32_t(kStemPatchPx * 4), uint32_t(kStemPatchRows), 1};
+    uint32_t es[4] = {1, 1, 1, 1};
+    bool sok = encode(&pl->tmA, dt, 3, in, dims, str, box, es, 2, smsg);
+    if (sok) {
+      uint64_t od[4] = {uint64_t(g.Cout), uint64_t(g.Wo), uint64_t(g.Ho), uint64_t(g.B)};
+      uint64_t os[3] = {uint64_t(g.Cout) * 2, uint64_t(g.Wo) * g.Cout * 2, uint64_t(g.Ho) * g.Wo * g.Cout * 2};
+      uint32_t ob[4] = {64, uint32_t(kStemTW), uint32_t(kStemTH), 1};
+      sok = encode(&pl->tmOut, dt, 4, e.out, od, os, ob, es, 0, smsg);
+    }
+    if (!sok) { delete pl; return failmsg(smsg); }
+    pl->tmW = pl->tmOut; pl->tmAct = pl->tmOut; pl->tmRes = pl->tmOut;
+    return pl;
+  }
   {
     // 3x3 / stride 1 / pad 1 on 64 or 128 input channels with a plain (bias, ReLU) epilogue: halo kernel
     const char* henv = std::getenv("B200RN_HALO");
@@ -1087,6 +1411,11 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       hp.total_tiles = hp.tiles_w * hp.tiles_h * g.B * hp.n_tiles;
       hp.relu = e.relu;
       hp.bias = e.bias;
+      if (const char* v = std::getenv("B200RN_DBG_SKIP")) hp.dbg_skip = std::atoi(v);
+      if (std::getenv("B200RN_DBG_TRACE")) {
+        cudaMalloc(&hp.trace, 64 * 8 * sizeof(unsigned long long));
+        cudaMemset(hp.trace, 0, 64 * 8 * sizeof(unsigned long long));
+      }
       const int sms = sm_count();
       int grid = std::min(hp.total_tiles, sms);
       grid = std::max(hp.n_tiles, (grid / hp.n_tiles) * hp.n_tiles);
@@ -1169,7 +1498,38 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   return pl;
 }
 
-void umma_conv_plan_destroy(UmmaConvPlan* p) { delete p; }
+void umma_conv_plan_destroy(UmmaConvPlan* p) {
+  if (p && !p->halo && p->p.trace) {
+    std::vector<unsigned long long> h(64 * 8);
+    cudaDeviceSynchronize();
+    cudaMemcpy(h.data(), p->p.trace, h.size() * 8, cudaMemcpyDeviceToHost);
+    unsigned long long t0 = h[0];
+    std::fprintf(stderr, "generic kernel, k_iters %d kgroup %d stages %d bn %d bstat %d grid %d tiles %d\n", p->p.num_k_iters, p->p.kgroup,
+                 p->p.num_stages, p->block_n, p->p.b_stationary, p->grid, p->p.total_tiles);
+    std::fprintf(stderr, "tile: first_load_issue | mma_top got_tmem got_first_stage all_issued | epi_top epi_got_acc epi_end (cycles)\n");
+    for (int i = 0; i < 20; ++i) {
+      std::fprintf(stderr, "%2d:", i);
+      for (int k = 0; k < 8; ++k) std::fprintf(stderr, " %8lld", h[i * 8 + k] ? (long long)(h[i * 8 + k] - t0) : -1LL);
+      std::fprintf(stderr, "\n");
+    }
+    cudaFree(p->p.trace);
+  }
+  if (p && p->halo && p->hp.trace) {
+    // timeline experiment: print CTA 0's per-tile stamps (cycles relative to the first)
+    std::vector<unsigned long long> h(64 * 8);
+    cudaDeviceSynchronize();
+    cudaMemcpy(h.data(), p->hp.trace, h.size() * 8, cudaMemcpyDeviceToHost);
+    unsigned long long t0 = h[0];
+    std::fprintf(stderr, "tile: load_issue | mma_wait_begin mma_got_halo mma_issued after_commit1 after_commit2 | tile_top after_tmem_empty (cycles)\n");
+    for (int i = 0; i < 24; ++i) {
+      std::fprintf(stderr, "%2d:", i);
+      for (int k = 0; k < 8; ++k) std::fprintf(stderr, " %8lld", h[i * 8 + k] ? (long long)(h[i * 8 + k] - t0) : -1LL);
+      std::fprintf(stderr, "\n");
+    }
+    cudaFree(p->hp.trace);
+  }
+  delete p;
+}
 
 cudaError_t umma_take_timeout_flag(unsigned int* flag) {
   *flag = 0;

@@ -202,6 +202,12 @@ struct b200rn {
           const PlanTensor& in = plan.tensors[size_t(L.in)];
           ConvGeom g{1, in.H, in.W, L.Cin, 0, 0, L.Cout, L.kh, L.kw, L.stride, L.pad};
           D.stem = (plan.layers[size_t(in.def_layer)].kind == LayerKind::InputXform && in.Cpad == 4) ? 1 : 0;
+          if (D.stem) {
+            // 2 = dedicated stem7x7_kernel (one input patch per tile); 1 = generic kernel over a 5-D overlapping view
+            const char* sv = std::getenv("B200RN_STEM_V2");
+            const bool plain = L.out >= 0 && L.out_act < 0 && L.in2 < 0 && L.pre_scale.empty();
+            if (plain && !(sv && sv[0] == '0')) D.stem = 2;
+          }
           char why[256];
           if (!umma_conv_supported(g, D.stem, why, sizeof why))
             throw ArgFail{fmt("layer '%s' cannot run in a 16-bit tensor-core mode: %s (use B200RN_MODE_EXACT)", L.name.c_str(), why)};
@@ -716,16 +722,18 @@ int b200rn_stem_conv(int dtype, const float* d_in_nchw, int B, int H, int W, con
     CK(cudaMalloc(&frame, fbytes));
     CK(cudaMemset(frame, 0, fbytes));
     CK(launch_input_xform(d_in_nchw, frame, dt, B, 3, H, W, 4, Hp, Wp, 3, 3, ds, dsh, 0, 0));
-    size_t bytes = umma_weight_bytes(g, 1);
+    const char* sv = std::getenv("B200RN_STEM_V2");
+    const int stem_mode = (sv && sv[0] == '0') ? 1 : 2;      // same choice as the engine makes
+    size_t bytes = umma_weight_bytes(g, stem_mode);
     std::vector<uint8_t> packed(bytes);
-    umma_pack_weights(w, g, dt, 1, packed.data());
+    umma_pack_weights(w, g, dt, stem_mode, packed.data());
     void* dw = nullptr;
     CK(cudaMalloc(&dw, bytes));
     CK(cudaMemcpy(dw, packed.data(), bytes, cudaMemcpyHostToDevice));
     Epilogue e;
     e.bias = db; e.relu = relu; e.out = d_out;
     char msg[512] = {0};
-    UmmaConvPlan* up = umma_conv_plan_create(dt, g, frame, dw, e, 1, msg, sizeof msg);
+    UmmaConvPlan* up = umma_conv_plan_create(dt, g, frame, dw, e, stem_mode, msg, sizeof msg);
     cudaError_t le = cudaSuccess, se = cudaSuccess;
     unsigned int flag = 0;
     if (up) {
