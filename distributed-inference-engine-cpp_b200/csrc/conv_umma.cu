@@ -1008,6 +1008,195 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
   if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
 }
 
+// ---- two M tiles per weight tile ("dual-M") ----------------------------------------------------------
+// The large-K layers of stages 3 and 4 (1x1 1024->256, 3x3 256->256, 1x1 2048->512, ...) are bound by the
+// L2 -> shared-memory feed: every 128-pixel tile streams the whole weight slab of its N tile again
+// (measured ~7 TB/s aggregate, profiles/).  Here one CTA works on TWO M tiles at once: each pipeline stage holds
+// A0 | A1 | B and the B tile is used by eight MMAs (four into accumulator D0, four into D1), so the bytes
+// staged per output tile drop from A+B to A+B/2 (1.5x less at N = 256).  Both accumulators fill TMEM
+// (2 x BLOCK_N columns), so the epilogue of an item does not overlap the next item's MMAs; with K >= 512 the
+// main loop dominates.  Epilogue: bias + optional ReLU, one output (the only form these layers need).
+struct DualParams {
+  int num_k_iters, cblks, kw, stride, pad;
+  int bw, bh, bn, tiles_w, tiles_h, m_tiles, n_tiles, total_items, num_stages, relu;
+  uint32_t a_bytes, b_bytes;
+  const float* bias;
+};
+
+template <typename T, int BLOCK_N>
+__global__ void __launch_bounds__(kBaseThreads, 1)
+conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                  const __grid_constant__ CUtensorMap tmOut, const DualParams p) {
+  constexpr int kChunks = BLOCK_N / 64;
+  constexpr uint32_t A_BYTES = kTileM * 128;
+  constexpr uint32_t B_BYTES = BLOCK_N * 128;
+  constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + B_BYTES;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int S = p.num_stages;
+  uint8_t* pipe = smem;
+  uint8_t* outbuf = pipe + S * STAGE_BYTES;        // two 16 KB chunk buffers, used alternately
+  float* s_bias = reinterpret_cast<float*>(outbuf + 2 * kChunkBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_bias + BLOCK_N);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + S;
+  uint64_t* tmem_full = empty_bar + S;
+  uint64_t* tmem_empty = tmem_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int my_items = (int(blockIdx.x) < p.total_items) ? (p.total_items - 1 - int(blockIdx.x)) / int(gridDim.x) + 1 : 0;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmW);
+    prefetch_tmap(&tmOut);
+    for (int i = 0; i < S; ++i) { mbar_init(smem_u32(&full_bar[i]), 1); mbar_init(smem_u32(&empty_bar[i]), 1); }
+    mbar_init(smem_u32(tmem_full), 1);
+    mbar_init(smem_u32(tmem_empty), kEpiThreads);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * BLOCK_N);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // M tile index -> patch origin; an index past the last tile lands beyond the batch, where TMA loads read
+  // zeros and TMA stores are clipped
+  auto m_coord = [&](int mt, int& w0, int& h0, int& n0) {
+    const int tw = mt % p.tiles_w; mt /= p.tiles_w;
+    const int th = mt % p.tiles_h;
+    w0 = tw * p.bw; h0 = th * p.bh; n0 = (mt / p.tiles_h) * p.bn;
+  };
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < my_items; ++i) {
+        const int item = int(blockIdx.x) + i * int(gridDim.x);
+        const int col0 = (item % p.n_tiles) * BLOCK_N;
+        const int pm = item / p.n_tiles;
+        int w0[2], h0[2], n0[2];
+        m_coord(2 * pm, w0[0], h0[0], n0[0]);
+        m_coord(2 * pm + 1, w0[1], h0[1], n0[1]);
+        for (int it = 0; it < p.num_k_iters; ++it) {
+          mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
+          const uint32_t fb = smem_u32(&full_bar[stage]);
+          const uint32_t dst = smem_u32(pipe + stage * STAGE_BYTES);
+          mbar_expect_tx(fb, 2 * p.a_bytes + p.b_bytes);
+          const int tap = it / p.cblks, cb = it - tap * p.cblks;
+          const int ky = tap / p.kw, kx = tap - ky * p.kw;
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            tma_load_4d(dst + h * A_BYTES, &tmA, fb, cb * 64, w0[h] * p.stride - p.pad + kx, h0[h] * p.stride - p.pad + ky, n0[h]);
+          tma_load_2d(dst + 2 * A_BYTES, &tmW, fb, it * 64, col0);
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc<T, BLOCK_N>();
+    constexpr uint32_t desc_hi = smem_desc_hi<128>();
+    if (elect_one()) {
+      const uint32_t pipe_lo = smem_desc_lo(smem_u32(pipe));
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < my_items; ++i) {
+        mbar_wait(smem_u32(tmem_empty), (uint32_t(i) & 1) ^ 1);      // epilogue has drained both accumulators
+        tc_fence_after();
+        for (int it = 0; it < p.num_k_iters; ++it) {
+          mbar_wait(smem_u32(&full_bar[stage]), phase);
+          tc_fence_after();
+          const uint32_t a_lo = pipe_lo + uint32_t(stage) * (STAGE_BYTES >> 4);
+          const uint32_t b_lo = a_lo + 2 * (A_BYTES >> 4);
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma_f16_lo(tmem_base + uint32_t(h * BLOCK_N), a_lo + h * (A_BYTES >> 4) + 2 * k, b_lo + 2 * k, desc_hi, idesc,
+                          (it | k) != 0 ? 1u : 0u);
+          umma_commit(smem_u32(&empty_bar[stage]));
+          if (it == p.num_k_iters - 1) umma_commit(smem_u32(tmem_full));
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else {
+    const int q4 = warp & 3;
+    const int g = (warp - 2) >> 2;
+    const int row = q4 * 32 + lane;
+    const int sw = row & 7;
+    const int et = threadIdx.x - 64;
+    const bool store_thread = (warp == 2 && lane == 0);
+    int cur_ntile = -1;
+    int cc = 0;                                  // running chunk counter: staging buffer = cc & 1
+    for (int i = 0; i < my_items; ++i) {
+      const int item = int(blockIdx.x) + i * int(gridDim.x);
+      const int n_tile = item % p.n_tiles;
+      const int col0 = n_tile * BLOCK_N;
+      const int pm = item / p.n_tiles;
+      if (n_tile != cur_ntile) {
+        cur_ntile = n_tile;
+        asm volatile("bar.sync 1, 256;" ::: "memory");      // nobody still reads the previous bias set
+        for (int k = et; k < BLOCK_N; k += kEpiThreads) s_bias[k] = __ldg(p.bias + col0 + k);
+      }
+      mbar_wait(smem_u32(tmem_full), uint32_t(i) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        int w0, h0, n0;
+        m_coord(2 * pm + h, w0, h0, n0);
+#pragma unroll 1
+        for (int c = 0; c < kChunks; ++c, ++cc) {
+          uint32_t acc[32];
+          tmem_ld_32x32b_x32(tmem_base + (uint32_t(q4 * 32) << 16) + uint32_t(h * BLOCK_N + c * 64 + g * 32), acc);
+          tmem_ld_wait();
+          if (h == 1 && c == kChunks - 1) {
+            tc_fence_before();
+            mbar_arrive(smem_u32(tmem_empty));
+          }
+          // the buffer about to be rewritten was stored two chunks ago: let only the latest store pend
+          if (store_thread && cc >= 2) tma_store_wait_read_pending<1>();
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          uint8_t* stage_out = outbuf + (cc & 1) * kChunkBytes;
+          uint4* out_row = reinterpret_cast<uint4*>(stage_out + row * 128);
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const int j = g * 4 + jj;
+            const int col = c * 64 + j * 8;
+            const float4 b0 = *reinterpret_cast<const float4*>(s_bias + col);
+            const float4 b1 = *reinterpret_cast<const float4*>(s_bias + col + 4);
+            float v[8];
+            v[0] = __uint_as_float(acc[jj * 8 + 0]) + b0.x; v[1] = __uint_as_float(acc[jj * 8 + 1]) + b0.y;
+            v[2] = __uint_as_float(acc[jj * 8 + 2]) + b0.z; v[3] = __uint_as_float(acc[jj * 8 + 3]) + b0.w;
+            v[4] = __uint_as_float(acc[jj * 8 + 4]) + b1.x; v[5] = __uint_as_float(acc[jj * 8 + 5]) + b1.y;
+            v[6] = __uint_as_float(acc[jj * 8 + 6]) + b1.z; v[7] = __uint_as_float(acc[jj * 8 + 7]) + b1.w;
+            if (p.relu) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+            }
+            out_row[j ^ sw] = make_uint4(pack2<T>(v[0], v[1]), pack2<T>(v[2], v[3]), pack2<T>(v[4], v[5]), pack2<T>(v[6], v[7]));
+          }
+          fence_proxy_async_smem();
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          if (store_thread) {
+            tma_store_4d(&tmOut, smem_u32(stage_out), col0 + c * 64, w0, h0, n0);
+            tma_store_commit();
+          }
+        }
+      }
+    }
+    if (store_thread) tma_store_wait_read();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
+}
+
 // ---- host side --------------------------------------------------------------------------------
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -1077,6 +1266,8 @@ struct UmmaConvPlan {
   int grid;
   int halo = 0;           // 3x3/s1/p1 layer routed to conv3x3_halo_kernel (tmA = patch map, tmOut = row-store map)
   HaloParams hp;
+  int dual = 0;           // large-K layer routed to conv_dualm_kernel (two M tiles per weight tile)
+  DualParams dp;
   int stem2 = 0;          // stem routed to stem7x7_kernel (tmA = patch map, tmOut = {64, 8, 16, 1} store map)
   Stem2Params sp;
 };
@@ -1319,8 +1510,27 @@ static cudaError_t launch_stem2(const UmmaConvPlan* pl, cudaStream_t s) {
   return cudaGetLastError();
 }
 
+template <typename T, int BLOCK_N>
+static cudaError_t launch_dual(const UmmaConvPlan* pl, cudaStream_t s) {
+  auto kern = conv_dualm_kernel<T, BLOCK_N>;
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    configured_device = dev;
+  }
+  kern<<<pl->grid, kBaseThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmOut, pl->dp);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
   const bool bf = pl->dt == DType::BF16;
+  if (pl->dual) {
+    if (pl->block_n == 128) return bf ? launch_dual<__nv_bfloat16, 128>(pl, s) : launch_dual<__half, 128>(pl, s);
+    return bf ? launch_dual<__nv_bfloat16, 256>(pl, s) : launch_dual<__half, 256>(pl, s);
+  }
   if (pl->stem2) return bf ? launch_stem2<__nv_bfloat16>(pl, s) : launch_stem2<__half>(pl, s);
   if (pl->halo) {
     if (pl->block_n == 64) return bf ? launch_halo<__nv_bfloat16, 64>(pl, s) : launch_halo<__half, 64>(pl, s);
@@ -1457,6 +1667,34 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   }
   plan_geometry(*pl);
   const int bw = p.bw, bh = p.bh, bn = p.bn;
+  {
+    // Large-K layer with a plain epilogue: consider two M tiles per weight tile.  Same cost model as the N-tile
+    // choice: (rounds over the SMs) x (bytes staged per K block) must come out lower than the single-M plan's.
+    const char* denv = std::getenv("B200RN_DUALM");
+    const int m_tiles = p.tiles_w * p.tiles_h * ((g.B + bn - 1) / bn);
+    if (!(denv && denv[0] == '0') && !stem_mode && p.has_out && !p.has_res && !p.has_act && !p.has_pre &&
+        p.num_k_iters >= 8 && (pl->block_n == 256 || pl->block_n == 128) && m_tiles >= 2) {
+      const int sms = sm_count();
+      const long items = long((m_tiles + 1) / 2) * p.n_tiles;
+      const long cost_dual = ((items + sms - 1) / sms) * long(2 * kTileM + pl->block_n);
+      const long cost_single = ((long(p.total_tiles) + sms - 1) / sms) * long(kTileM + pl->block_n);
+      const uint32_t stage_bytes = uint32_t(2 * kTileM * 128 + pl->block_n * 128);
+      const uint32_t fixed = 1024u + 2 * kChunkBytes + uint32_t(pl->block_n) * 4 + 8u * (2 * 8 + 2) + 64;
+      const int stages = int((227u * 1024 - fixed) / stage_bytes);
+      if (cost_dual < cost_single && stages >= 2) {
+        DualParams& dp = pl->dp;
+        std::memset(&dp, 0, sizeof dp);
+        pl->dual = 1;
+        dp.num_k_iters = p.num_k_iters; dp.cblks = p.cblks; dp.kw = p.kw; dp.stride = p.stride; dp.pad = p.pad;
+        dp.bw = bw; dp.bh = bh; dp.bn = bn; dp.tiles_w = p.tiles_w; dp.tiles_h = p.tiles_h;
+        dp.m_tiles = m_tiles; dp.n_tiles = p.n_tiles; dp.total_items = int(items);
+        dp.num_stages = std::min(stages, 6);
+        dp.relu = p.relu; dp.a_bytes = p.a_bytes; dp.b_bytes = p.b_bytes; dp.bias = p.bias;
+        pl->smem_bytes = fixed + uint32_t(dp.num_stages) * stage_bytes;
+        pl->grid = int(std::min<long>(items, sms));
+      }
+    }
+  }
 
   std::string msg;
   bool ok = true;
@@ -1495,6 +1733,11 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   if (ok) ok = encode_act(&pl->tmAct, dt, e.out_act ? e.out_act : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
   if (ok) ok = encode_act(&pl->tmRes, dt, e.residual ? e.residual : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
   if (!ok) { delete pl; return failmsg(msg); }
+  if (std::getenv("B200RN_VERBOSE"))
+    std::fprintf(stderr, "[b200rn] conv %dx%d s%d %d->%d @%dx%d B%d: %s bn=%d patch=%dx%dx%d tiles=%d grid=%d stages=%d kgroup=%d bstat=%d smem=%u\n",
+                 g.kh, g.kw, g.stride, g.Cin, g.Cout, g.H, g.W, g.B, pl->dual ? "dual-M" : "generic", pl->block_n, bw, bh, bn,
+                 pl->dual ? pl->dp.total_items : p.total_tiles, pl->grid, pl->dual ? pl->dp.num_stages : p.num_stages, p.kgroup,
+                 p.b_stationary, pl->smem_bytes);
   return pl;
 }
 

@@ -132,5 +132,8 @@ CONV_CASES = [
     ("3x3 s1 64->128 @30x17 B3 (halo, ragged)", dict(B=3, H=30, W=17, Cin=64, Cout=128, k=3, stride=1, pad=1)),
     ("3x3 s1 128->64 @14 B7 (halo)", dict(B=7, H=14, W=14, Cin=128, Cout=64, k=3, stride=1, pad=1, relu=1)),
     ("3x3 s1 64->64 @56 B9 (halo, many tiles)", dict(B=9, H=56, W=56, Cin=64, Cout=64, k=3, stride=1, pad=1, relu=1)),
+    ("1x1 512->256 @7 B1024 (dual-M)", dict(B=1024, H=7, W=7, Cin=512, Cout=256, k=1, stride=1, pad=0, relu=1)),
+    ("3x3 64->256 @7 B1000 (dual-M, odd tile count)", dict(B=1000, H=7, W=7, Cin=64, Cout=256, k=3, stride=1, pad=1, relu=1)),
+    ("1x1 s2 1024->512 @14 B300 (dual-M, no relu)", dict(B=300, H=14, W=14, Cin=1024, Cout=512, k=1, stride=2, pad=0)),
     ("3x3 s1 256->256 @14 B64 (N=256 tiles)", dict(B=64, H=14, W=14, Cin=256, Cout=256, k=3, stride=1, pad=1, relu=1)),
 ]
