@@ -317,8 +317,20 @@ def main():
         conv_flops = sum(l["flops"] for l in conv)
         total_ms = sum(l["ms"] for l in layers)
         achieved = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
-        roof = {"bound": "tensor", "kernel": "conv_umma_kernel (53 launches/step)", "achieved": achieved,
-                "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"], "traffic": None,
+        # DRAM bytes of the same 53 launches from the committed ncu pass (profiles/, tools/ncu_summary.py);
+        # measured once per profile run at batch 256 fp16, not live
+        traffic, traffic_src = None, None
+        try:
+            with open(os.path.join(ROOT, "profiles", "r1_conv_traffic.json")) as f:
+                tj = json.load(f)
+            if B == 256 and args.mode == "fp16":
+                traffic, traffic_src = tj["conv_dram_bytes_per_step"], "profiles/r1_conv_traffic.json (ncu dram__bytes_read+write, sum over the 53 conv launches of one step)"
+        except Exception:
+            pass
+        roof = {"bound": "tensor", "kernel": "tcgen05 conv kernels (53 launches/step: conv_umma, conv_dualm, conv3x3_halo, stem7x7)",
+                "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
+                "traffic": traffic, "traffic_source": traffic_src,
+                "algorithmic_bytes": sum(l["bytes"] for l in conv),
                 "peak_source": pk["source"], "conv_share_of_step": conv_ms / total_ms if total_ms else None,
                 "conv_ms_per_step": conv_ms, "all_layers_ms_per_step": total_ms}
         # the memory-bound side, against the measured copy bandwidth

@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Condenses ncu reports / CSV logs into the small text files kept under profiles/.
     python tools/ncu_summary.py rep <file.ncu-rep> [...]      # key metrics per captured kernel (markdown)
-    python tools/ncu_summary.py launches <launches.csv>       # per-launch device time + share of the step
+    python tools/ncu_summary.py launches <launches.csv> [traffic.json]   # per-launch time, DRAM bytes, tensor %
 """
 import csv
 import io
@@ -45,36 +45,60 @@ def rep(paths):
             print()
 
 
-def launches(path):
+def launches(path, traffic_json=None):
     rows = [r for r in csv.reader(open(path)) if r and not r[0].startswith("==")]
     hdr = rows[0]
-    iname, ival, iid = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("ID")
-    items = []
+    iname, imet, iunit, ival, iid = (hdr.index("Kernel Name"), hdr.index("Metric Name"), hdr.index("Metric Unit"),
+                                     hdr.index("Metric Value"), hdr.index("ID"))
+    per = {}
     for r in rows[1:]:
         try:
-            items.append((int(r[iid]), r[iname], float(r[ival].replace(",", ""))))
+            v = float(r[ival].replace(",", ""))
         except ValueError:
             continue
-    unit = rows[1][hdr.index("Metric Unit")] if len(rows) > 1 else "ns"
-    scale = {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(unit, 1e-3)
-    tot = sum(v for _, _, v in items) * scale
-    print("# ncu launch list: %d launches, %.1f us total (cold-cache, serialised: compare shares, not absolutes)\n" % (len(items), tot))
+        d = per.setdefault(int(r[iid]), {"name": r[iname]})
+        m = r[imet]
+        if m == "gpu__time_duration.sum":
+            v *= {"ns": 1e-3, "us": 1.0, "ms": 1e3, "nsecond": 1e-3, "usecond": 1.0, "msecond": 1e3}.get(r[iunit], 1e-3)
+        if m.startswith("dram__bytes"):
+            v *= {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(r[iunit], 1.0)
+        d[m] = v
+
+    def short(n):
+        return n.split("(")[0].replace("void rn::<unnamed>::", "").replace("void unnamed>::", "").replace("void rn::", "")
+
+    items = [per[k] for k in sorted(per)]
+    tot = sum(d.get("gpu__time_duration.sum", 0.0) for d in items)
+    print("# ncu launch list: %d launches of one forward step (batch 256, fp16), %.1f us total\n" % (len(items), tot))
+    print("Cold-cache, serialised launches: compare SHARES with the CUDA-event numbers, not absolutes.\n")
     by = {}
-    for _, n, v in items:
-        key = n.split("(")[0].replace("void rn::<unnamed>::", "").replace("void rn::", "")
-        by.setdefault(key, [0, 0.0])
-        by[key][0] += 1
-        by[key][1] += v * scale
-    print("| kernel | launches | us | share |\n|---|---|---|---|")
-    for k, (c, v) in sorted(by.items(), key=lambda x: -x[1][1]):
-        print("| %s | %d | %.1f | %.1f%% |" % (k, c, v, 100 * v / tot))
-    print("\n| # | kernel | us |\n|---|---|---|")
-    for i, (idx, n, v) in enumerate(items):
-        print("| %d | %s | %.1f |" % (i, n.split("(")[0].replace("void rn::<unnamed>::", "").replace("void rn::", "")[:70], v * scale))
+    for d in items:
+        k = short(d["name"])
+        b = by.setdefault(k, [0, 0.0, 0.0])
+        b[0] += 1
+        b[1] += d.get("gpu__time_duration.sum", 0.0)
+        b[2] += d.get("dram__bytes_read.sum", 0.0) + d.get("dram__bytes_write.sum", 0.0)
+    print("| kernel | launches | us | share | DRAM bytes (read+write) |\n|---|---|---|---|---|")
+    for k, (c, v, t) in sorted(by.items(), key=lambda x: -x[1][1]):
+        print("| %s | %d | %.1f | %.1f%% | %.1f MB |" % (k, c, v, 100 * v / tot, t / 1e6))
+    print("\n| # | kernel | us | DRAM read MB | DRAM write MB | DRAM %% of peak | tensor pipe %% |\n|---|---|---|---|---|---|---|")
+    for i, d in enumerate(items):
+        print("| %d | %s | %.1f | %.1f | %.1f | %.1f | %.1f |" % (
+            i, short(d["name"])[:60], d.get("gpu__time_duration.sum", 0.0), d.get("dram__bytes_read.sum", 0.0) / 1e6,
+            d.get("dram__bytes_write.sum", 0.0) / 1e6, d.get("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", 0.0),
+            d.get("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", 0.0)))
+    if traffic_json:
+        import json
+        conv = [d for d in items if any(t in d["name"] for t in ("conv_umma", "halo", "stem7x7", "dualm"))]
+        out = {"source": path.split("/")[-1], "conv_launches_per_step": len(conv),
+               "conv_dram_bytes_per_step": sum(d.get("dram__bytes_read.sum", 0.0) + d.get("dram__bytes_write.sum", 0.0) for d in conv),
+               "all_dram_bytes_per_step": sum(d.get("dram__bytes_read.sum", 0.0) + d.get("dram__bytes_write.sum", 0.0) for d in items),
+               "conv_us_per_step_under_ncu": sum(d.get("gpu__time_duration.sum", 0.0) for d in conv)}
+        json.dump(out, open(traffic_json, "w"), indent=1)
 
 
 if __name__ == "__main__":
     if sys.argv[1] == "rep":
         rep(sys.argv[2:])
     else:
-        launches(sys.argv[2])
+        launches(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else None)
