@@ -1197,6 +1197,8 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
 }
 
+#include "conv_tail.cuh"
+
 // ---- host side --------------------------------------------------------------------------------
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -1270,6 +1272,10 @@ struct UmmaConvPlan {
   DualParams dp;
   int stem2 = 0;          // stem routed to stem7x7_kernel (tmA = patch map, tmOut = {64, 8, 16, 1} store map)
   Stem2Params sp;
+  int tail = 0;           // 1x1 conv + residual fused with the following 1x1 conv (conv_tail_kernel)
+  TailParams tp;
+  CUtensorMap tmW1, tmOut1;
+  int tp_n1 = 0;
 };
 
 bool umma_conv_supported(const ConvGeom& g, int stem_mode, char* why, size_t cap) {
@@ -1525,8 +1531,27 @@ static cudaError_t launch_dual(const UmmaConvPlan* pl, cudaStream_t s) {
   return cudaGetLastError();
 }
 
+template <typename T, int N1>
+static cudaError_t launch_tail(const UmmaConvPlan* pl, cudaStream_t s) {
+  auto kern = conv_tail_kernel<T, N1>;
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    configured_device = dev;
+  }
+  kern<<<pl->grid, kBaseThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmW1, pl->tmRes, pl->tmOut, pl->tmOut1, pl->tp);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
   const bool bf = pl->dt == DType::BF16;
+  if (pl->tail) {
+    if (pl->tp_n1 == 64) return bf ? launch_tail<__nv_bfloat16, 64>(pl, s) : launch_tail<__half, 64>(pl, s);
+    return bf ? launch_tail<__nv_bfloat16, 128>(pl, s) : launch_tail<__half, 128>(pl, s);
+  }
   if (pl->dual) {
     if (pl->block_n == 128) return bf ? launch_dual<__nv_bfloat16, 128>(pl, s) : launch_dual<__half, 128>(pl, s);
     return bf ? launch_dual<__nv_bfloat16, 256>(pl, s) : launch_dual<__half, 256>(pl, s);
@@ -1567,6 +1592,65 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   p.pre_scale = e.pre_scale; p.pre_shift = e.pre_shift;
   if (p.has_pre && (stem_mode || g.kh != 1 || g.kw != 1 || g.pad != 0)) { delete pl; return failmsg("operand prologue needs a 1x1, pad-0 conv"); }
   if (!p.has_out && !p.has_act) { delete pl; return failmsg("conv with no output"); }
+  if (e.tail_out) {
+    // 1x1 conv (Cout 256) + residual -> raw output, and the following 1x1 conv on relu(bn(.)) of it
+    if (stem_mode || g.kh != 1 || g.kw != 1 || g.stride != 1 || g.pad != 0 || g.Cout != kTailN3 || !p.has_res || !p.has_out ||
+        p.has_act || p.has_pre || !e.act_scale || !e.act_shift || !e.tail_w || !e.tail_bias ||
+        (e.tail_cout != 64 && e.tail_cout != 128)) {
+      delete pl;
+      return failmsg("fused tail conv needs a 1x1/s1/p0 conv to 256 channels with a residual and a raw output, and a 64- or 128-channel tail");
+    }
+    TailParams& tp = pl->tp;
+    std::memset(&tp, 0, sizeof tp);
+    pl->tail = 1; pl->tp_n1 = e.tail_cout; pl->kb = 128; pl->block_n = kTailN3;
+    int bw = 1, bh = 1, bn = 1;
+    choose_patch(g.B, g.Ho, g.Wo, bw, bh, bn);
+    tp.cblks = g.Cin / 64;
+    tp.bw = bw; tp.bh = bh; tp.bn = bn;
+    tp.tiles_w = (g.Wo + bw - 1) / bw; tp.tiles_h = (g.Ho + bh - 1) / bh;
+    tp.total_tiles = tp.tiles_w * tp.tiles_h * ((g.B + bn - 1) / bn);
+    tp.rows = uint32_t(bw * bh * bn);
+    tp.relu = e.relu; tp.act_relu = e.act_relu; tp.tail_relu = e.tail_relu;
+    tp.bias = e.bias; tp.act_scale = e.act_scale; tp.act_shift = e.act_shift; tp.tail_bias = e.tail_bias;
+    if (std::getenv("B200RN_DBG_TRACE")) {
+      cudaMalloc(&tp.trace, 64 * 8 * sizeof(unsigned long long));
+      cudaMemset(tp.trace, 0, 64 * 8 * sizeof(unsigned long long));
+    }
+    const uint32_t fixed = 1024u + uint32_t(tp.cblks) * kTailN3 * 128 + 4u * uint32_t(e.tail_cout) * 128 +
+                           uint32_t(e.tail_cout / 64) * kChunkBytes + (3u * kTailN3 + uint32_t(e.tail_cout)) * 4 + 8u * 32 + 64;
+    const int slots = (int(227u * 1024) - int(fixed)) / int(kChunkBytes);    // 16 KB units left for the three rings
+    tp.act_bufs = 2;
+    tp.a_stages = slots - 2 >= 6 * tp.cblks ? 2 : 1;
+    tp.r_slots = std::min(8, slots - 2 - tp.a_stages * tp.cblks);
+    if (slots < 2 + tp.cblks + 2 || tp.r_slots < 2) { delete pl; return failmsg("fused tail conv: shared memory does not hold the weights plus staging"); }
+    pl->smem_bytes = fixed + uint32_t(tp.act_bufs + tp.a_stages * tp.cblks + tp.r_slots) * kChunkBytes;
+    pl->grid = std::min(tp.total_tiles, sm_count());
+    std::string tmsg;
+    bool tok = encode_act(&pl->tmA, dt, in, g.B, g.H, g.W, g.Cin, bw, bh, bn, 1, tmsg);
+    if (tok) {
+      uint64_t wd[2] = {uint64_t(g.Cin), uint64_t(kTailN3)};
+      uint64_t ws[1] = {uint64_t(g.Cin) * 2};
+      uint32_t wb[2] = {64, uint32_t(kTailN3)};
+      uint32_t we[2] = {1, 1};
+      tok = encode(&pl->tmW, dt, 2, w_packed, wd, ws, wb, we, false, tmsg);
+    }
+    if (tok) {
+      uint64_t wd[2] = {uint64_t(kTailN3), uint64_t(e.tail_cout)};
+      uint64_t ws[1] = {uint64_t(kTailN3) * 2};
+      uint32_t wb[2] = {64, uint32_t(e.tail_cout)};
+      uint32_t we[2] = {1, 1};
+      tok = encode(&pl->tmW1, dt, 2, e.tail_w, wd, ws, wb, we, false, tmsg);
+    }
+    if (tok) tok = encode_act(&pl->tmRes, dt, e.residual, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, tmsg);
+    if (tok) tok = encode_act(&pl->tmOut, dt, e.out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, tmsg);
+    if (tok) tok = encode_act(&pl->tmOut1, dt, e.tail_out, g.B, g.Ho, g.Wo, e.tail_cout, bw, bh, bn, 1, tmsg);
+    if (!tok) { delete pl; return failmsg(tmsg); }
+    pl->tmAct = pl->tmOut;
+    if (std::getenv("B200RN_VERBOSE"))
+      std::fprintf(stderr, "[b200rn] conv 1x1 %d->%d + tail ->%d @%dx%d B%d: patch=%dx%dx%d tiles=%d grid=%d a_stages=%d r_slots=%d smem=%u\n",
+                   g.Cin, g.Cout, e.tail_cout, g.H, g.W, g.B, bw, bh, bn, tp.total_tiles, pl->grid, tp.a_stages, tp.r_slots, pl->smem_bytes);
+    return pl;
+  }
   if (stem_mode == 2) {
     if (!p.has_out || p.has_res || p.has_act || p.has_pre) { delete pl; return failmsg("stem kernel supports bias + ReLU + one output only"); }
     Stem2Params& sp = pl->sp;
@@ -1742,6 +1826,21 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
 }
 
 void umma_conv_plan_destroy(UmmaConvPlan* p) {
+  if (p && p->tail && p->tp.trace) {
+    std::vector<unsigned long long> h(64 * 8);
+    cudaDeviceSynchronize();
+    cudaMemcpy(h.data(), p->tp.trace, h.size() * 8, cudaMemcpyDeviceToHost);
+    unsigned long long t0 = h[0];
+    std::fprintf(stderr, "tail kernel, chunk: top | got residual+acc | math+smem writes done | fenced | barrier | store issued, prev store read (cycles)\n");
+    for (int i = 0; i < 40; ++i) {
+      std::fprintf(stderr, "%2d:", i);
+      for (int k = 0; k < 6; ++k) std::fprintf(stderr, " %8lld", h[i * 8 + k] ? (long long)(h[i * 8 + k] - t0) : -1LL);
+      std::fprintf(stderr, "\n");
+    }
+    cudaFree(p->tp.trace);
+    delete p;
+    return;
+  }
   if (p && !p->halo && p->p.trace) {
     std::vector<unsigned long long> h(64 * 8);
     cudaDeviceSynchronize();

@@ -45,6 +45,12 @@ bool prologue_enabled() {
   return v && v[0] == '1';
 }
 
+// Tail fusion (plan.h): on unless B200RN_TAIL=0; tensor-core modes only.
+bool tail_enabled() {
+  const char* v = std::getenv("B200RN_TAIL");
+  return !(v && v[0] == '0');
+}
+
 struct CudaFail { std::string msg; };
 #define CK(expr)                                                                                       \
   do {                                                                                                 \
@@ -64,6 +70,8 @@ struct DevLayer {
   float* pre_scale = nullptr;
   float* pre_shift = nullptr;
   void* w = nullptr;
+  void* tail_w = nullptr;               // fused tail conv: packed weights + bias
+  float* tail_bias = nullptr;
   bool umma = false;
   int stem = 0;
   float* splitk = nullptr;              // Gemm only: split-K partial sums + tile counters
@@ -113,7 +121,7 @@ struct b200rn {
     cudaSetDevice(device);
     for (auto& L : dl) {
       cudaFree(L.bias); cudaFree(L.act_scale); cudaFree(L.act_shift); cudaFree(L.w); cudaFree(L.splitk);
-      cudaFree(L.pre_scale); cudaFree(L.pre_shift);
+      cudaFree(L.pre_scale); cudaFree(L.pre_shift); cudaFree(L.tail_w); cudaFree(L.tail_bias);
       for (auto& kv : L.plans) umma_conv_plan_destroy(kv.second);
     }
     cudaFree(arena);
@@ -180,7 +188,7 @@ struct b200rn {
 
   void build(const std::string& path) {
     OnnxModel model = load_onnx(path);
-    plan = build_plan(model, dt == DType::F32 ? 4 : 8, prologue_enabled());
+    plan = build_plan(model, dt == DType::F32 ? 4 : 8, prologue_enabled(), dt != DType::F32 && tail_enabled());
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&s_h2d, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&s_compute, cudaStreamNonBlocking));
@@ -218,6 +226,16 @@ struct b200rn {
           CK(cudaMalloc(&D.w, bytes));
           CK(cudaMemcpy(D.w, packed.data(), bytes, cudaMemcpyHostToDevice));
           D.weight_bytes = double(bytes);
+          if (L.tail_out >= 0) {
+            ConvGeom tg{1, in.H, in.W, L.Cout, in.H, in.W, L.tail_Cout, 1, 1, 1, 0};
+            size_t tbytes = umma_weight_bytes(tg, 0);
+            std::vector<uint8_t> tpacked(tbytes);
+            umma_pack_weights(L.tail_weight.data(), tg, dt, 0, tpacked.data());
+            CK(cudaMalloc(&D.tail_w, tbytes));
+            CK(cudaMemcpy(D.tail_w, tpacked.data(), tbytes, cudaMemcpyHostToDevice));
+            D.tail_bias = upload(L.tail_bias);
+            D.weight_bytes += double(tbytes);
+          }
           if (D.stem) stem_tensor = L.in;
         } else {
           // fp32 CUDA-core path wants W^T: [K][Cout]
@@ -284,6 +302,11 @@ struct b200rn {
         ConvGeom g = geom(L, B);
         e.residual = tptr(L.in2);
         e.pre_scale = D.pre_scale; e.pre_shift = D.pre_shift; e.pre_relu = L.pre_relu;
+        if (L.tail_out >= 0) {
+          if (!D.umma) throw ArgFail{fmt("layer '%s': a fused tail conv only exists on the tensor-core path", L.name.c_str())};
+          e.tail_w = D.tail_w; e.tail_bias = D.tail_bias; e.tail_out = out_ptr(L.tail_out);
+          e.tail_cout = L.tail_Cout; e.tail_relu = L.tail_relu;
+        }
         if (D.umma) {
           UmmaConvPlan*& up = D.plans[B];
           if (!up) {
@@ -552,7 +575,7 @@ int64_t b200rn_describe_plan(const char* onnx_path, int mode, char* buf, size_t 
   std::string text;
   int rc = guarded(nullptr, [&] {
     OnnxModel m = load_onnx(onnx_path);
-    Plan p = build_plan(m, mode == B200RN_MODE_EXACT ? 4 : 8, prologue_enabled());
+    Plan p = build_plan(m, mode == B200RN_MODE_EXACT ? 4 : 8, prologue_enabled(), mode != B200RN_MODE_EXACT && tail_enabled());
     text = p.describe();
   });
   if (rc != B200RN_OK) return -1;
@@ -608,7 +631,7 @@ int b200rn_profile_layers(b200rn_t* h, const float* d_nchw, size_t batch, int it
       if (flops) flops[li] = 2.0 * L.macs_per_sample * double(batch);
       if (bytes) {
         double b = h->dl[size_t(li)].weight_bytes;
-        for (int t : {L.in, L.in2, L.out, L.out_act})
+        for (int t : {L.in, L.in2, L.out, L.out_act, L.tail_out})
           if (t >= 0) {
             const PlanTensor& T = h->plan.tensors[size_t(t)];
             b += double(T.elems_per_sample()) * double(batch) * double(h->elsize(T));
@@ -700,6 +723,55 @@ int b200rn_conv2d(int dtype, const void* d_in, int B, int H, int W, int Cin, con
       }
     }
     cudaFree(dw); cudaFree(db); cudaFree(ds); cudaFree(dsh);
+  });
+}
+
+int b200rn_conv1x1_tail(int dtype, const void* d_in, int B, int H, int W, int Cin, const float* w, const float* bias, int relu,
+                        const void* d_residual, void* d_out, const float* act_scale, const float* act_shift, int act_relu,
+                        const float* tail_w, const float* tail_bias, int tail_cout, int tail_relu, void* d_tail_out) {
+  if (!d_in || !w || !d_residual || !d_out || !act_scale || !act_shift || !tail_w || !d_tail_out || dtype < 1 || dtype > 2) {
+    g_error = "b200rn_conv1x1_tail: bad argument";
+    return B200RN_ERR_ARG;
+  }
+  return guarded(nullptr, [&] {
+    DType dt = DType(dtype);
+    const int Cout = 256;
+    ConvGeom g{B, H, W, Cin, H, W, Cout, 1, 1, 1, 0};
+    ConvGeom tg{B, H, W, Cout, H, W, tail_cout, 1, 1, 1, 0};
+    std::vector<float> hb(size_t(Cout), 0.f), htb(size_t(tail_cout), 0.f);
+    if (bias) hb.assign(bias, bias + Cout);
+    if (tail_bias) htb.assign(tail_bias, tail_bias + tail_cout);
+    struct Bufs {
+      void* p[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+      ~Bufs() { for (void* q : p) cudaFree(q); }
+    } bufs;
+    bufs.p[0] = upload(hb); bufs.p[1] = upload(htb);
+    bufs.p[2] = upload(std::vector<float>(act_scale, act_scale + Cout));
+    bufs.p[3] = upload(std::vector<float>(act_shift, act_shift + Cout));
+    auto pack = [&](const float* src, const ConvGeom& cg, void*& dst) {
+      size_t bytes = umma_weight_bytes(cg, 0);
+      std::vector<uint8_t> packed(bytes);
+      umma_pack_weights(src, cg, dt, 0, packed.data());
+      CK(cudaMalloc(&dst, bytes));
+      CK(cudaMemcpy(dst, packed.data(), bytes, cudaMemcpyHostToDevice));
+    };
+    pack(w, g, bufs.p[4]);
+    pack(tail_w, tg, bufs.p[5]);
+    Epilogue e;
+    e.bias = static_cast<float*>(bufs.p[0]); e.relu = relu; e.residual = d_residual; e.out = d_out;
+    e.act_scale = static_cast<float*>(bufs.p[2]); e.act_shift = static_cast<float*>(bufs.p[3]); e.act_relu = act_relu;
+    e.tail_w = bufs.p[5]; e.tail_bias = static_cast<float*>(bufs.p[1]); e.tail_out = d_tail_out;
+    e.tail_cout = tail_cout; e.tail_relu = tail_relu;
+    char msg[512] = {0};
+    UmmaConvPlan* up = umma_conv_plan_create(dt, g, d_in, bufs.p[4], e, 0, msg, sizeof msg);
+    if (!up) throw CudaFail{std::string("b200rn_conv1x1_tail: ") + msg};
+    cudaError_t le = launch_conv_umma(up, 0);
+    cudaError_t se = cudaDeviceSynchronize();
+    umma_conv_plan_destroy(up);
+    unsigned int flag = 0;
+    if (se == cudaSuccess) se = umma_take_timeout_flag(&flag);
+    if (le != cudaSuccess || se != cudaSuccess || flag)
+      throw CudaFail{fmt("b200rn_conv1x1_tail: launch %s / sync %s / barrier timeout %u", cudaGetErrorString(le), cudaGetErrorString(se), flag)};
   });
 }
 

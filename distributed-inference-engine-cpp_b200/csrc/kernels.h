@@ -30,6 +30,14 @@ struct Epilogue {
   const float* act_shift = nullptr;
   int relu = 0;
   int act_relu = 0;
+  // Fused tail (tensor-core path only): a following 1x1 / stride-1 conv that is the only reader of out_act.
+  //   tail_out[m][n] = tail_relu ? max(sum_c act(v)[m][c] * tail_w[n][c] + tail_bias[n], 0) : ...
+  // where act(v) is the out_act expression above, kept in shared memory; out_act itself must be null.
+  const void* tail_w = nullptr;       // packed like any 1x1 conv's weights (umma_pack_weights)
+  const float* tail_bias = nullptr;
+  void* tail_out = nullptr;
+  int tail_cout = 0;
+  int tail_relu = 0;
 };
 
 struct ConvGeom {

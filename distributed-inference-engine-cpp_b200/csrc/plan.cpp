@@ -41,6 +41,7 @@ struct Builder {
   const OnnxModel& m;
   int align;
   bool consumer_prologue = true;
+  bool tail_fusion = false;
   std::map<std::string, PendingPrologue> prologues;   // activated value name -> how to make it on the fly
   Plan plan;
   std::map<std::string, std::vector<int>> consumers;  // value name -> node indices
@@ -470,8 +471,42 @@ struct Builder {
     emit(std::move(L));
   }
 
+  // End of one bottleneck block + start of the next: the wide 1x1 conv's activated output feeds exactly one
+  // narrow 1x1 conv.  Decided from reader counts and shapes only.
+  void fuse_tails() {
+    auto& Ls = plan.layers;
+    for (size_t i = 0; i < Ls.size(); ++i) {
+      PlanLayer& L = Ls[i];
+      if (L.kind != LayerKind::Conv || L.out < 0 || L.out_act < 0 || L.in2 < 0 || L.tail_out >= 0) continue;
+      if (L.kh != 1 || L.kw != 1 || L.stride != 1 || L.pad != 0 || !L.pre_scale.empty()) continue;
+      if (L.Cout != 256 || L.Cin != 64) continue;
+      if (L.out_act == value_or(plan.output_name)) continue;
+      int readers = 0, j = -1;
+      for (size_t k = 0; k < Ls.size(); ++k)
+        for (int t : {Ls[k].in, Ls[k].in2})
+          if (t == L.out_act) { ++readers; j = int(k); }
+      if (readers != 1 || j <= int(i)) continue;
+      PlanLayer& M = Ls[size_t(j)];
+      if (M.kind != LayerKind::Conv || M.in != L.out_act || M.in2 >= 0 || M.out < 0 || M.out_act >= 0) continue;
+      if (M.kh != 1 || M.kw != 1 || M.stride != 1 || M.pad != 0 || !M.pre_scale.empty() || M.tail_out >= 0) continue;
+      if (M.Cin != L.Cout || (M.Cout != 64 && M.Cout != 128)) continue;
+      L.tail_out = M.out; L.tail_Cout = M.Cout; L.tail_relu = M.relu;
+      L.tail_weight = std::move(M.weight); L.tail_bias = std::move(M.bias);
+      L.macs_per_sample += M.macs_per_sample;
+      L.name += "+" + M.name;
+      L.out_act = -1;
+      Ls.erase(Ls.begin() + j);
+    }
+  }
+  int value_or(const std::string& name) const {
+    auto it = value.find(name);
+    return it == value.end() ? -2 : it->second;
+  }
+
   Plan finish() {
     for (int li : order) plan.layers.push_back(std::move(layers[size_t(li)]));
+    plan.output_name = m.outputs[0].name;
+    if (tail_fusion) fuse_tails();
     const auto& out = m.outputs[0];
     auto it = value.find(out.name);
     if (it == value.end()) fail("graph output '" + out.name + "' is not produced by a supported node");
@@ -495,7 +530,7 @@ struct Builder {
         if (T.def_layer < 0) fail("internal: layer '" + L.name + "' reads '" + T.name + "' before it is produced");
         T.last_use = int(i);
       }
-      for (int t : {L.out, L.out_act}) {
+      for (int t : {L.out, L.out_act, L.tail_out}) {
         if (t < 0) continue;
         PlanTensor& T = plan.tensors[size_t(t)];
         if (T.def_layer < 0) { T.def_layer = int(i); T.last_use = std::max(T.last_use, int(i)); }
@@ -527,8 +562,9 @@ struct Builder {
 
 }  // namespace
 
-Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue) {
+Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue, bool tail_fusion) {
   Builder b(model, channel_align, consumer_prologue);
+  b.tail_fusion = tail_fusion;
   return b.run();
 }
 
@@ -547,6 +583,7 @@ std::string Plan::describe() const {
     const PlanLayer& L = layers[i];
     os << i << " " << layer_kind_name(L.kind) << " in=" << tn(L.in) << " in2=" << tn(L.in2) << " out=" << tn(L.out)
        << " out_act=" << tn(L.out_act);
+    if (L.tail_out >= 0) os << " tail_out=" << tn(L.tail_out) << " tail_cout=" << L.tail_Cout;
     if (L.kind == LayerKind::Conv)
       os << " k=" << L.kh << "x" << L.kw << " s=" << L.stride << " p=" << L.pad << " cin=" << L.Cin << " cout=" << L.Cout;
     if (L.kind == LayerKind::MaxPool) os << " k=" << L.pool_k << " s=" << L.pool_stride << " p=" << L.pool_pad;

@@ -12,6 +12,7 @@
 //   T -> BN -> ReLU       (T made by Conv/MaxPool)    : otherwise a second epilogue output relu(s*T+t);
 //                                                       the raw T is not written if nothing else reads it
 //   input -> BN           (BN the only consumer)      : applied while re-laying NCHW fp32 -> NHWC
+//   wide 1x1 Conv(+Add) -> BN -> ReLU -> 1x1 Conv     : (tail_fusion) both convs in one launch, see PlanLayer::tail_*
 //   BN -> ReLU -> GlobalAveragePool                    : affine+ReLU applied inside the pooling kernel
 // Anything else falls back to a stand-alone element-wise layer; an operator outside the
 // supported set is an error (no CPU fallback).
@@ -58,6 +59,14 @@ struct PlanLayer {
   // activated copy of the tensor is never written to memory)
   std::vector<float> pre_scale, pre_shift;
   bool pre_relu = false;
+  // Conv tail: the 1x1 / stride-1 / pad-0 conv that was the only reader of this layer's activated output, run
+  // inside the same launch on the activated tile while it is still in shared memory.  out_act is then -1
+  // (act_scale / act_shift / act_relu still describe the activation between the two convs) and
+  //   tail_out = tail_relu ? max(conv1x1(act, tail_weight) + tail_bias, 0) : ...
+  int tail_out = -1, tail_Cout = 0;
+  std::vector<float> tail_weight;  // [tail_Cout][Cout]
+  std::vector<float> tail_bias;
+  bool tail_relu = false;
   // MaxPool
   int pool_k = 0, pool_stride = 0, pool_pad = 0;
   double macs_per_sample = 0;  // algorithmic multiply-accumulates (Conv/Gemm), for rooflines
@@ -80,6 +89,9 @@ struct Plan {
 // 8 for 16-bit paths; the 3-channel network input is always stored as 4).
 // consumer_prologue: fuse "T -> BN -> ReLU -> {1x1 pad-0 convs}" into those convs' operand load instead
 // of a second output of T's producer (saves writing and re-reading the activated copy).
-Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue = false);
+// tail_fusion: fuse "Conv(1x1, Cin 64 -> 256 channels, + residual) -> BN -> ReLU -> Conv 1x1 (<= 128 channels)"
+// pairs -- the end of one bottleneck block and the start of the next -- into one launch when that second conv
+// is the activated tensor's only reader (tensor-core modes only: the shapes are what conv_tail_kernel takes).
+Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue = false, bool tail_fusion = false);
 
 }  // namespace rn

@@ -130,6 +130,15 @@ int b200rn_conv2d(int dtype, const void* d_in, int B, int H, int W, int Cin, con
                   int Cout, int kh, int kw, int stride, int pad, int relu, const void* d_residual, void* d_out,
                   void* d_out_act, const float* act_scale, const float* act_shift, int act_relu,
                   const float* pre_scale, const float* pre_shift, int pre_relu);
+/* The fused pair "1x1 conv (Cin -> Cout = 256) + residual, then the next block's 1x1 conv (256 -> tail_cout)"
+ * as one launch (tensor-core dtypes 1 / 2 only; the graph planner's tail fusion, csrc/plan.h).  Replaces two
+ * ORT Conv nodes + Add + BatchNormalization + Relu of the reference's session (src/inference_engine.cpp:134).
+ *   d_out      = conv1x1(d_in, w, bias) (ReLU'd if relu) + d_residual                       [B,H,W,256]
+ *   d_tail_out = relu?( conv1x1( relu?(act_scale*d_out + act_shift), tail_w ) + tail_bias )   [B,H,W,tail_cout]
+ * w: [256][Cin], tail_w: [tail_cout][256] fp32 host arrays; tail_cout is 64 or 128; Cin is 64. */
+int b200rn_conv1x1_tail(int dtype, const void* d_in, int B, int H, int W, int Cin, const float* w, const float* bias, int relu,
+                        const void* d_residual, void* d_out, const float* act_scale, const float* act_shift, int act_relu,
+                        const float* tail_w, const float* tail_bias, int tail_cout, int tail_relu, void* d_tail_out);
 /* Same, for the 7x7/2 stem through the tensor-core path: d_in_nchw is fp32 NCHW [B,3,H,W]; the
  * input re-layout (with per-channel scale/shift) and the conv run back to back. */
 int b200rn_stem_conv(int dtype, const float* d_in_nchw, int B, int H, int W, const float* in_scale,

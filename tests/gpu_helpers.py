@@ -78,6 +78,59 @@ def conv_case(dtype, B, H, W, Cin, Cout, k, stride, pad, relu=0, residual=False,
     return out
 
 
+def tail_case(dtype, B, H, W, tail_cout=64, relu=0, act_relu=1, tail_relu=1, seed=0, Cin=64):
+    """Runs b200rn_conv1x1_tail (1x1 conv to 256 ch + residual, then the next 1x1 conv on relu(bn(.))) on random
+    data; compares both outputs with a float64 CPU evaluation on the same rounded operands."""
+    g = torch.Generator().manual_seed(seed)
+    tdt = TORCH_DT[dtype]
+    Cout = 256
+    x = torch.randn(B, Cin, H, W, generator=g).to(tdt)
+    w = (torch.randn(Cout, Cin, 1, 1, generator=g) * (2.0 / Cin) ** 0.5).to(tdt)
+    bias = torch.randn(Cout, generator=g) * 0.5
+    res = torch.randn(B, Cout, H, W, generator=g).to(tdt)
+    s2 = torch.rand(Cout, generator=g) + 0.5
+    t2 = torch.randn(Cout, generator=g) * 0.3
+    w1 = (torch.randn(tail_cout, Cout, 1, 1, generator=g) * (2.0 / Cout) ** 0.5).to(tdt)
+    bias1 = torch.randn(tail_cout, generator=g) * 0.5
+    y = F.conv2d(x.double(), w.double(), bias.double())
+    if relu:
+        y = y.clamp_min(0)
+    y = y + res.double()
+    a = y * s2.double().view(1, -1, 1, 1) + t2.double().view(1, -1, 1, 1)
+    if act_relu:
+        a = a.clamp_min(0)
+    a = a.to(tdt).double()                     # the activated tile is held in the 16-bit storage type
+    u = F.conv2d(a, w1.double(), bias1.double())
+    if tail_relu:
+        u = u.clamp_min(0)
+    d_x = x.permute(0, 2, 3, 1).contiguous().cuda()
+    d_res = res.permute(0, 2, 3, 1).contiguous().cuda()
+    d_out = torch.full((B, H, W, Cout), float("nan"), dtype=tdt, device="cuda")
+    d_tail = torch.full((B, H, W, tail_cout), float("nan"), dtype=tdt, device="cuda")
+    f32 = lambda t: np.ascontiguousarray(t.float().numpy().astype(np.float32))
+    w_np, w1_np = f32(w.view(Cout, Cin)), f32(w1.view(tail_cout, Cout))
+    b_np, b1_np, s_np, t_np = f32(bias), f32(bias1), f32(s2), f32(t2)
+    torch.cuda.synchronize()
+    rc = lib.b200rn_conv1x1_tail(dtype, d_x.data_ptr(), B, H, W, Cin, pkg.fptr(w_np), pkg.fptr(b_np), relu, d_res.data_ptr(),
+                                 d_out.data_ptr(), pkg.fptr(s_np), pkg.fptr(t_np), act_relu, pkg.fptr(w1_np), pkg.fptr(b1_np),
+                                 tail_cout, tail_relu, d_tail.data_ptr())
+    out = {"rc": rc, "msg": lib.b200rn_global_error().decode() if rc else ""}
+    if rc:
+        return out
+    rtol, atol = TOL[dtype]
+
+    def cmp(dev, ref):
+        got = dev.float().cpu().permute(0, 3, 1, 2).double()
+        bad = ~torch.isfinite(got)
+        err = (got - ref).abs()
+        lim = atol + rtol * ref.abs()
+        return {"max_err": float(err[~bad].max()) if (~bad).any() else float("nan"), "nonfinite": int(bad.sum()),
+                "viol": int((err > lim).sum() + bad.sum()), "n": got.numel()}
+    out["out"] = cmp(d_out, y)
+    out["tail"] = cmp(d_tail, u)
+    return out
+
+
 def stem_case(dtype, B, H, W, Cout=64, seed=0):
     g = torch.Generator().manual_seed(seed)
     tdt = TORCH_DT[dtype]

@@ -67,6 +67,7 @@ def test_missing_or_malformed_model_is_an_error(tmp_path):
 @pytest.mark.parametrize("prologue", [False, True])
 def test_plan_resnet50(r50_model, prologue, monkeypatch):
     monkeypatch.setenv("B200RN_PROLOGUE", "1" if prologue else "0")
+    monkeypatch.setenv("B200RN_TAIL", "0")
     text = pkg.describe_plan(r50_model, "fp16")
     lines = text.strip().splitlines()
     head, layers = lines[0], lines[1:]
@@ -91,6 +92,24 @@ def test_plan_resnet50(r50_model, prologue, monkeypatch):
     shapes = set(re.search(r"k=(\dx\d) s=(\d) p=(\d) cin=(\d+) cout=(\d+)", l).groups() +
                  (re.search(r"in=t\d+\[\d+x(\d+)x", l).group(1),) for l in convs)
     assert len(shapes) == 23                                # 23 unique conv shapes
+
+
+def test_plan_resnet50_tail_fusion(r50_model, monkeypatch):
+    """Default 16-bit plan: at 56x56 the wide 1x1 conv (+residual) that ends a block and the narrow 1x1 conv that
+    starts the next run as one launch; the exact (fp32 CUDA-core) plan is never fused that way."""
+    monkeypatch.delenv("B200RN_TAIL", raising=False)
+    monkeypatch.setenv("B200RN_PROLOGUE", "0")
+    lines = pkg.describe_plan(r50_model, "fp16").strip().splitlines()
+    head, layers = lines[0], lines[1:]
+    assert "macs/sample=4089184256" in head and len(layers) == 55
+    fused = [l for l in layers if "tail_out=t" in l]
+    assert len(fused) == 2
+    for l in fused:
+        assert "cin=64 cout=256" in l and "tail_cout=64" in l and "out_act=-" in l and "in2=t" in l
+        assert re.search(r"in=t\d+\[64x56x56\]", l) and re.search(r"tail_out=t\d+\[64x56x56\]", l)
+        assert "stage1_conv" in l and l.count("_conv") == 2       # two ONNX Conv nodes in one launch
+    exact = pkg.describe_plan(r50_model, "exact").strip().splitlines()[1:]
+    assert len(exact) == 57 and not any("tail_out" in l for l in exact)
 
 
 def test_cpp_parser_matches_python_reader(tiny_model):
