@@ -172,6 +172,20 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)
         "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
       : "r"(taddr));
 }
+// shared-memory accesses by 32-bit shared-space address (LDS / STS instead of generic loads through a 64-bit pointer)
+__device__ __forceinline__ uint4 lds_u4(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_u4(uint32_t a, uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 __device__ __forceinline__ bool elect_one() {
@@ -1542,7 +1556,7 @@ static cudaError_t launch_tail(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  kern<<<pl->grid, kBaseThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmW1, pl->tmRes, pl->tmOut, pl->tmOut1, pl->tp);
+  kern<<<pl->grid, kTailThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmW1, pl->tmRes, pl->tmOut, pl->tmOut1, pl->tp);
   return cudaGetLastError();
 }
 
@@ -1613,14 +1627,14 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     tp.relu = e.relu; tp.act_relu = e.act_relu; tp.tail_relu = e.tail_relu;
     tp.bias = e.bias; tp.act_scale = e.act_scale; tp.act_shift = e.act_shift; tp.tail_bias = e.tail_bias;
     if (std::getenv("B200RN_DBG_TRACE")) {
-      cudaMalloc(&tp.trace, 64 * 8 * sizeof(unsigned long long));
-      cudaMemset(tp.trace, 0, 64 * 8 * sizeof(unsigned long long));
+      cudaMalloc(&tp.trace, 8 * 32 * 8 * sizeof(unsigned long long));
+      cudaMemset(tp.trace, 0, 8 * 32 * 8 * sizeof(unsigned long long));
     }
     const uint32_t fixed = 1024u + uint32_t(tp.cblks) * kTailN3 * 128 + 4u * uint32_t(e.tail_cout) * 128 +
-                           uint32_t(e.tail_cout / 64) * kChunkBytes + (3u * kTailN3 + uint32_t(e.tail_cout)) * 4 + 8u * 32 + 64;
+                           uint32_t(e.tail_cout / 64) * kChunkBytes + (3u * kTailN3 + uint32_t(e.tail_cout)) * 4 + 8u * 48 + 64;
     const int slots = (int(227u * 1024) - int(fixed)) / int(kChunkBytes);    // 16 KB units left for the three rings
     tp.act_bufs = 2;
-    tp.a_stages = slots - 2 >= 6 * tp.cblks ? 2 : 1;
+    tp.a_stages = 1;     // the next tile's operand is only needed a tile from now; the slots are worth more in the residual ring
     tp.r_slots = std::min(8, slots - 2 - tp.a_stages * tp.cblks);
     if (slots < 2 + tp.cblks + 2 || tp.r_slots < 2) { delete pl; return failmsg("fused tail conv: shared memory does not hold the weights plus staging"); }
     pl->smem_bytes = fixed + uint32_t(tp.act_bufs + tp.a_stages * tp.cblks + tp.r_slots) * kChunkBytes;
@@ -1827,14 +1841,19 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
 
 void umma_conv_plan_destroy(UmmaConvPlan* p) {
   if (p && p->tail && p->tp.trace) {
-    std::vector<unsigned long long> h(64 * 8);
+    std::vector<unsigned long long> h(8 * 32 * 8);
     cudaDeviceSynchronize();
     cudaMemcpy(h.data(), p->tp.trace, h.size() * 8, cudaMemcpyDeviceToHost);
-    unsigned long long t0 = h[0];
-    std::fprintf(stderr, "tail kernel, chunk: top | got residual+acc | math+smem writes done | fenced | barrier | store issued, prev store read (cycles)\n");
-    for (int i = 0; i < 40; ++i) {
-      std::fprintf(stderr, "%2d:", i);
-      for (int k = 0; k < 6; ++k) std::fprintf(stderr, " %8lld", h[i * 8 + k] ? (long long)(h[i * 8 + k] - t0) : -1LL);
+    unsigned long long t0 = std::min(h[0], h[size_t(32 + 1) * 8]);
+    std::fprintf(stderr, "tail kernel, CTA 0, first warp of each epilogue group, per chunk: top | buffers ready | - | - | tmem + residual read | "
+                         "math + smem writes | signalled | tail tile done (cycles)\n");
+    for (int i = 8; i < 28; ++i) {
+      const int w = i & 1;
+      std::fprintf(stderr, "chunk %2d group %d:", i, w);
+      for (int k = 0; k < 8; ++k) {
+        unsigned long long v = h[(size_t(w) * 32 + i) * 8 + k];
+        std::fprintf(stderr, " %7lld", v ? (long long)(v - t0) : -1LL);
+      }
       std::fprintf(stderr, "\n");
     }
     cudaFree(p->tp.trace);
