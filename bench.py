@@ -327,7 +327,7 @@ def main():
                 traffic, traffic_src = tj["conv_dram_bytes_per_step"], "profiles/r1_conv_traffic.json (ncu dram__bytes_read+write, sum over the 53 conv launches of one step)"
         except Exception:
             pass
-        roof = {"bound": "tensor", "kernel": "tcgen05 conv kernels (53 launches/step: conv_umma, conv_dualm, conv3x3_halo, stem7x7)",
+        roof = {"bound": "tensor", "kernel": "tcgen05 conv kernels (53 launches/step: conv_umma, conv_wide, conv_tail, conv_dualm, conv3x3_halo, stem7x7)",
                 "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
                 "traffic": traffic, "traffic_source": traffic_src,
                 "algorithmic_bytes": sum(l["bytes"] for l in conv),

@@ -1212,6 +1212,7 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 }
 
 #include "conv_tail.cuh"
+#include "conv_wide.cuh"
 
 // ---- host side --------------------------------------------------------------------------------
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -1286,6 +1287,8 @@ struct UmmaConvPlan {
   DualParams dp;
   int stem2 = 0;          // stem routed to stem7x7_kernel (tmA = patch map, tmOut = {64, 8, 16, 1} store map)
   Stem2Params sp;
+  int wide = 0;           // epilogue-bound 1x1 conv with a 256-wide N tile routed to conv_wide_kernel
+  WideParams wp;
   int tail = 0;           // 1x1 conv + residual fused with the following 1x1 conv (conv_tail_kernel)
   TailParams tp;
   CUtensorMap tmW1, tmOut1;
@@ -1560,8 +1563,24 @@ static cudaError_t launch_tail(const UmmaConvPlan* pl, cudaStream_t s) {
   return cudaGetLastError();
 }
 
+template <typename T>
+static cudaError_t launch_wide(const UmmaConvPlan* pl, cudaStream_t s) {
+  auto kern = conv_wide_kernel<T>;
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    configured_device = dev;
+  }
+  kern<<<pl->grid, kWideThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->wp);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
   const bool bf = pl->dt == DType::BF16;
+  if (pl->wide) return bf ? launch_wide<__nv_bfloat16>(pl, s) : launch_wide<__half>(pl, s);
   if (pl->tail) {
     if (pl->tp_n1 == 64) return bf ? launch_tail<__nv_bfloat16, 64>(pl, s) : launch_tail<__half, 64>(pl, s);
     return bf ? launch_tail<__nv_bfloat16, 128>(pl, s) : launch_tail<__half, 128>(pl, s);
@@ -1763,6 +1782,69 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       return pl;
     }
   }
+  {
+    // Block-ending 1x1 convs (wide output + residual, raw and/or activated copy written): conv_wide_kernel.
+    // Measured per layer at batch 256 (B200RN_WIDE=0/1): the residual layers gain up to 21 % (most where only the
+    // activated copy is written), the projection shortcuts (no residual, one output) lose 15-20 % against the
+    // generic kernel's stationary-weight path, so those and the plain 1x1 convs stay where they were.
+    // B200RN_WIDE=2 routes every wide-output 1x1 conv here (tests).
+    const char* wenv = std::getenv("B200RN_WIDE");
+    const bool wide_all = wenv && wenv[0] == '2';
+    if (!(wenv && wenv[0] == '0') && !stem_mode && !p.has_pre && g.kh == 1 && g.kw == 1 && g.pad == 0 && g.Cout % kWideN == 0 &&
+        (p.has_res || (wide_all && (p.has_act || g.Cout > g.Cin)))) {
+      WideParams& wp = pl->wp;
+      std::memset(&wp, 0, sizeof wp);
+      pl->wide = 1; pl->kb = 128; pl->block_n = kWideN;
+      int bw = 1, bh = 1, bn = 1;
+      choose_patch(g.B, g.Ho, g.Wo, bw, bh, bn);
+      wp.cblks = g.Cin / 64; wp.num_k_iters = wp.cblks; wp.kw = 1; wp.stride = g.stride; wp.pad = 0;
+      wp.bw = bw; wp.bh = bh; wp.bn = bn;
+      wp.tiles_w = (g.Wo + bw - 1) / bw; wp.tiles_h = (g.Ho + bh - 1) / bh;
+      wp.m_tiles = wp.tiles_w * wp.tiles_h * ((g.B + bn - 1) / bn);
+      wp.n_tiles = g.Cout / kWideN;
+      wp.has_res = p.has_res; wp.has_out = p.has_out; wp.has_act = p.has_act; wp.relu = p.relu; wp.act_relu = p.act_relu;
+      wp.rows = uint32_t(bw * bh * bn); wp.a_bytes = wp.rows * 128u;
+      wp.bias = e.bias; wp.act_scale = e.act_scale; wp.act_shift = e.act_shift;
+      if (std::getenv("B200RN_DBG_TRACE")) {
+        cudaMalloc(&wp.trace, 96 * 8 * sizeof(unsigned long long));
+        cudaMemset(wp.trace, 0, 96 * 8 * sizeof(unsigned long long));
+      }
+      const char* senv = std::getenv("B200RN_WIDE_STAGES");
+      wp.stages = senv ? std::max(2, std::min(3, std::atoi(senv))) : 2;
+      const uint32_t fixed = 1024u + 3u * kWideN * 4 + 8u * (2 * 3 + 4 + 32) + 64;
+      const int slots = (int(227u * 1024) - int(fixed)) / int(kChunkBytes) - 3 * wp.stages;   // 16 KB units left for the rings
+      const bool use_r = p.has_res || p.has_out;
+      if (use_r && p.has_act) { wp.c_slots = std::max(2, slots * 3 / 7); wp.r_slots = slots - wp.c_slots; }
+      else if (use_r) wp.r_slots = slots;
+      else wp.c_slots = slots;
+      wp.r_slots = std::min(8, wp.r_slots); wp.c_slots = std::min(8, wp.c_slots);
+      const int sms = sm_count();
+      const long total = long(wp.m_tiles) * wp.n_tiles;
+      int grid = int(std::min<long>(total, sms));
+      grid = std::max(wp.n_tiles, (grid / wp.n_tiles) * wp.n_tiles);
+      pl->grid = grid;
+      pl->smem_bytes = fixed + uint32_t(3 * wp.stages + (use_r ? wp.r_slots : 0) + (p.has_act ? wp.c_slots : 0)) * kChunkBytes;
+      std::string wmsg;
+      bool wok = encode_act(&pl->tmA, dt, in, g.B, g.H, g.W, g.Cin, bw, bh, bn, g.stride, wmsg);
+      if (wok) {
+        uint64_t wd[2] = {uint64_t(g.Cin), uint64_t(g.Cout)};
+        uint64_t ws[1] = {uint64_t(g.Cin) * 2};
+        uint32_t wb[2] = {64, uint32_t(kWideN)};
+        uint32_t we[2] = {1, 1};
+        wok = encode(&pl->tmW, dt, 2, w_packed, wd, ws, wb, we, false, wmsg);
+      }
+      const void* any_out = e.out ? e.out : e.out_act;
+      if (wok) wok = encode_act(&pl->tmOut, dt, any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, wmsg);
+      if (wok) wok = encode_act(&pl->tmAct, dt, e.out_act ? e.out_act : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, wmsg);
+      if (wok) wok = encode_act(&pl->tmRes, dt, e.residual ? e.residual : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, wmsg);
+      if (!wok) { delete pl; return failmsg(wmsg); }
+      if (std::getenv("B200RN_VERBOSE"))
+        std::fprintf(stderr, "[b200rn] conv 1x1 s%d %d->%d @%dx%d B%d: wide-epilogue patch=%dx%dx%d m_tiles=%d n_tiles=%d grid=%d stages=%d r_slots=%d c_slots=%d smem=%u\n",
+                     g.stride, g.Cin, g.Cout, g.H, g.W, g.B, bw, bh, bn, wp.m_tiles, wp.n_tiles, grid, wp.stages, wp.r_slots, wp.c_slots,
+                     pl->smem_bytes);
+      return pl;
+    }
+  }
   plan_geometry(*pl);
   const int bw = p.bw, bh = p.bh, bn = p.bn;
   {
@@ -1840,6 +1922,29 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
 }
 
 void umma_conv_plan_destroy(UmmaConvPlan* p) {
+  if (p && p->wide && p->wp.trace) {
+    std::vector<unsigned long long> h(96 * 8);
+    cudaDeviceSynchronize();
+    cudaMemcpy(h.data(), p->wp.trace, h.size() * 8, cudaMemcpyDeviceToHost);
+    const unsigned long long t0 = h[0];
+    auto rel = [&](unsigned long long v) { return v ? (long long)(v - t0) : -1LL; };
+    std::fprintf(stderr, "wide kernel CTA 0 (k_iters %d stages %d r_slots %d c_slots %d)\n", p->wp.num_k_iters, p->wp.stages, p->wp.r_slots, p->wp.c_slots);
+    std::fprintf(stderr, "MMA thread, per tile: top | accumulator free | K block 0..4 landed (cycles)\n");
+    for (int i = 0; i < 8; ++i) {
+      std::fprintf(stderr, "tile %2d:", i);
+      for (int k = 0; k < 7; ++k) std::fprintf(stderr, " %7lld", rel(h[size_t(i) * 8 + k]));
+      std::fprintf(stderr, "\n");
+    }
+    std::fprintf(stderr, "epilogue (first warp of the chunk's group), per chunk: top | slots ready | math + smem writes done | signalled ; tile top\n");
+    for (int cc = 0; cc < 32; ++cc) {
+      std::fprintf(stderr, "chunk %2d:", cc);
+      for (int k = 0; k < 4; ++k) std::fprintf(stderr, " %7lld", rel(h[size_t(32 + cc) * 8 + k]));
+      std::fprintf(stderr, " ; %7lld\n", rel(h[size_t(32 + cc) * 8 + 7]));
+    }
+    cudaFree(p->wp.trace);
+    delete p;
+    return;
+  }
   if (p && p->tail && p->tp.trace) {
     std::vector<unsigned long long> h(8 * 32 * 8);
     cudaDeviceSynchronize();

@@ -189,4 +189,19 @@ CONV_CASES = [
     ("3x3 64->256 @7 B1000 (dual-M, odd tile count)", dict(B=1000, H=7, W=7, Cin=64, Cout=256, k=3, stride=1, pad=1, relu=1)),
     ("1x1 s2 1024->512 @14 B300 (dual-M, no relu)", dict(B=300, H=14, W=14, Cin=1024, Cout=512, k=1, stride=2, pad=0)),
     ("3x3 s1 256->256 @14 B64 (N=256 tiles)", dict(B=64, H=14, W=14, Cin=256, Cout=256, k=3, stride=1, pad=1, relu=1)),
+    # wide-epilogue kernel (16-bit modes): every combination of residual / raw / activated outputs, one and many N
+    # tiles, fewer M tiles than CTAs per N tile, ragged patches, more tiles than a CTA's rings hold
+    ("wide 64->256 @56 B8 res raw+act", dict(B=8, H=56, W=56, Cin=64, Cout=256, k=1, stride=1, pad=0, residual=True,
+                                             want_out=True, want_act=True)),
+    ("wide 64->256 @56 B8 shortcut", dict(B=8, H=56, W=56, Cin=64, Cout=256, k=1, stride=1, pad=0)),
+    ("wide 256->1024 @14 B40 res raw+act", dict(B=40, H=14, W=14, Cin=256, Cout=1024, k=1, stride=1, pad=0, residual=True,
+                                                want_out=True, want_act=True)),
+    ("wide 256->1024 @14 B40 res act-only no-relu", dict(B=40, H=14, W=14, Cin=256, Cout=1024, k=1, stride=1, pad=0,
+                                                         residual=True, want_out=False, want_act=True, act_relu=0)),
+    ("wide 128->512 @28 B20 act-only no res", dict(B=20, H=28, W=28, Cin=128, Cout=512, k=1, stride=1, pad=0, relu=1,
+                                                   want_out=False, want_act=True)),
+    ("wide 512->2048 @7 B70 res raw+act (8 N tiles)", dict(B=70, H=7, W=7, Cin=512, Cout=2048, k=1, stride=1, pad=0,
+                                                           residual=True, want_out=True, want_act=True)),
+    ("wide s2 512->1024 @28 B9 shortcut", dict(B=9, H=28, W=28, Cin=512, Cout=1024, k=1, stride=2, pad=0)),
+    ("wide 64->256 @13x9 B3 ragged res raw", dict(B=3, H=13, W=9, Cin=64, Cout=256, k=1, stride=1, pad=0, residual=True)),
 ]

@@ -11,7 +11,9 @@ import gpu_helpers as gh  # noqa: E402
 
 @pytest.mark.parametrize("dtype", [0, 1, 2], ids=["fp32", "bf16", "fp16"])
 @pytest.mark.parametrize("name,kw", gh.CONV_CASES, ids=[c[0] for c in gh.CONV_CASES])
-def test_conv2d(dtype, name, kw):
+def test_conv2d(dtype, name, kw, monkeypatch):
+    if name.startswith("wide"):
+        monkeypatch.setenv("B200RN_WIDE", "2")      # also the residual-free shapes go through conv_wide_kernel
     r = gh.conv_case(dtype, **kw)
     assert r["rc"] == 0, r["msg"]
     for key in ("out", "act"):
