@@ -317,17 +317,17 @@ def main():
         conv_flops = sum(l["flops"] for l in conv)
         total_ms = sum(l["ms"] for l in layers)
         achieved = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
-        # DRAM bytes of the same 53 launches from the committed ncu pass (profiles/, tools/ncu_summary.py);
+        # DRAM bytes of the same conv launches from the committed ncu pass (profiles/, tools/ncu_summary.py);
         # measured once per profile run at batch 256 fp16, not live
         traffic, traffic_src = None, None
         try:
             with open(os.path.join(ROOT, "profiles", "r1_conv_traffic.json")) as f:
                 tj = json.load(f)
             if B == 256 and args.mode == "fp16":
-                traffic, traffic_src = tj["conv_dram_bytes_per_step"], "profiles/r1_conv_traffic.json (ncu dram__bytes_read+write, sum over the 53 conv launches of one step)"
+                traffic, traffic_src = tj["conv_dram_bytes_per_step"], "profiles/r1_conv_traffic.json (ncu dram__bytes_read+write, sum over the %d conv launches of one step)" % tj.get("conv_launches_per_step", len(conv))
         except Exception:
             pass
-        roof = {"bound": "tensor", "kernel": "tcgen05 conv kernels (53 launches/step: conv_umma, conv_wide, conv_tail, conv_dualm, conv3x3_halo, stem7x7)",
+        roof = {"bound": "tensor", "kernel": "tcgen05 conv kernels (%d launches/step: conv_umma, conv_wide, conv_tail, conv_dualm, conv3x3_halo, stem7x7)" % len(conv),
                 "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
                 "traffic": traffic, "traffic_source": traffic_src,
                 "algorithmic_bytes": sum(l["bytes"] for l in conv),
