@@ -35,6 +35,7 @@ struct TailParams {
   int cblks, bw, bh, bn, tiles_w, tiles_h, total_tiles;
   int a_stages, r_slots, act_bufs;
   int relu, act_relu, tail_relu;
+  int pf_dist;                 // residual L2 prefetch distance in tiles (0 = off)
   uint32_t rows;
   const float* bias;
   const float* act_scale;
@@ -134,8 +135,16 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int c = 0; c < kChunks; ++c) tma_load_2d(smem_u32(w1 + c * W1_BLOCK), &tmW1, wb, c * 64, 0);
       int stage = 0;
       uint32_t phase = 0, cc = 0;
+      // experiment knob (B200RN_TAIL_PF, default off): L2 prefetch of a later tile's residual; measured slower
+      auto prefetch_tile = [&](int t) {
+        if (t >= p.total_tiles || p.pf_dist == 0) return;
+        const TailTile pt = tail_decode(p, t);
+        for (int c = 0; c < kChunks; ++c) tma_prefetch_4d(&tmRes, c * 64, pt.w0, pt.h0, pt.n0);
+      };
+      for (int j = 0; j < p.pf_dist; ++j) prefetch_tile(int(blockIdx.x) + j * int(gridDim.x));
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
         const TailTile tc = tail_decode(p, tile);
+        prefetch_tile(tile + p.pf_dist * int(gridDim.x));
         mbar_wait(smem_u32(&a_empty[stage]), phase ^ 1);
         const uint32_t fb = smem_u32(&a_full[stage]);
         mbar_expect_tx(fb, uint32_t(p.cblks) * p.rows * 128u);

@@ -111,6 +111,12 @@ __device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* m, 
   asm volatile("cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
                ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4) : "memory");
 }
+// L2 prefetch of a box (no shared-memory destination, no barrier): hides HBM latency for data whose landing buffer
+// is not free yet
+__device__ __forceinline__ void tma_prefetch_4d(const CUtensorMap* m, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global [%0, {%1, %2, %3, %4}];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
 __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, uint32_t src, int c0, int c1, int c2, int c3) {
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
                ::"l"(reinterpret_cast<uint64_t>(m)), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
@@ -1644,6 +1650,10 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     tp.total_tiles = tp.tiles_w * tp.tiles_h * ((g.B + bn - 1) / bn);
     tp.rows = uint32_t(bw * bh * bn);
     tp.relu = e.relu; tp.act_relu = e.act_relu; tp.tail_relu = e.tail_relu;
+    {
+      const char* penv = std::getenv("B200RN_TAIL_PF");
+      tp.pf_dist = penv ? std::max(0, std::min(4, std::atoi(penv))) : 0;   // measured: 2 makes the layer 5 % slower
+    }
     tp.bias = e.bias; tp.act_scale = e.act_scale; tp.act_shift = e.act_shift; tp.tail_bias = e.tail_bias;
     if (std::getenv("B200RN_DBG_TRACE")) {
       cudaMalloc(&tp.trace, 8 * 32 * 8 * sizeof(unsigned long long));
@@ -1809,6 +1819,8 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
         cudaMalloc(&wp.trace, 96 * 8 * sizeof(unsigned long long));
         cudaMemset(wp.trace, 0, 96 * 8 * sizeof(unsigned long long));
       }
+      const char* penv = std::getenv("B200RN_WIDE_PF");
+      wp.pf_dist = penv ? std::max(0, std::min(4, std::atoi(penv))) : 0;   // measured: 2 costs 4 % of the whole step
       const char* senv = std::getenv("B200RN_WIDE_STAGES");
       wp.stages = senv ? std::max(2, std::min(3, std::atoi(senv))) : 2;
       const uint32_t fixed = 1024u + 3u * kWideN * 4 + 8u * (2 * 3 + 4 + 32) + 64;

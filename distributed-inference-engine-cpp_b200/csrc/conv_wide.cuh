@@ -27,6 +27,7 @@ struct WideParams {
   int bw, bh, bn, tiles_w, tiles_h, m_tiles, n_tiles;
   int stages, r_slots, c_slots;
   int has_res, has_out, has_act, relu, act_relu;
+  int pf_dist;                 // residual L2 prefetch distance in tiles (0 = off)
   uint32_t rows, a_bytes;
   const float* bias;
   const float* act_scale;
@@ -177,8 +178,17 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===== residual TMA producer (one thread): keeps the raw / residual ring full, a whole tile ahead of the epilogue =====
     if (use_r && elect_one()) {
       uint32_t cc = 0;
+      // Experiment knob (B200RN_WIDE_PF, default off): pull the residual of a later tile into L2 ahead of the ring's
+      // own load.  Measured at batch 256 it makes every residual layer 3-20 % slower, so it stays off.
+      auto prefetch_tile = [&](int j) {
+        if (!p.has_res || j >= my_tiles || p.pf_dist == 0) return;
+        const WideTile t = wide_decode(p, m_first + j * m_step);
+        for (int c = 0; c < kChunks; ++c) tma_prefetch_4d(&tmRes, col0 + c * 64, t.w0, t.h0, t.n0);
+      };
+      for (int j = 0; j < p.pf_dist; ++j) prefetch_tile(j);
       for (int i = 0; i < my_tiles; ++i) {
         const WideTile tc = wide_decode(p, m_first + i * m_step);
+        prefetch_tile(i + p.pf_dist);
         for (int c = 0; c < kChunks; ++c, ++cc) {
           const uint32_t slot = cc % uint32_t(SR);
           mbar_wait(smem_u32(&r_empty[slot]), ((cc / uint32_t(SR)) & 1) ^ 1);
