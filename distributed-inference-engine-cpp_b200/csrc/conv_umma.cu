@@ -1800,8 +1800,20 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     // B200RN_WIDE=2 routes every wide-output 1x1 conv here (tests).
     const char* wenv = std::getenv("B200RN_WIDE");
     const bool wide_all = wenv && wenv[0] == '2';
+    // "Deep" configuration for the large-K 1x1 convs with a plain epilogue: their main loop is bound by how many
+    // operand bytes are in flight (L2 latency ~2500 cycles x 41 B/clk with three 48 KB stages in the general
+    // kernel, whose whole-tile staging buffer takes the room a fourth would need).  Chunk-ring staging needs only
+    // two 16 KB slots, which leaves four stages.
+    const char* denv2 = std::getenv("B200RN_DEEP");
+    // Measured per layer at batch 256: 1x1 1024->256 @14x14 0.0455 -> 0.0422 ms, 512->256 @28x28 0.076 -> 0.068;
+    // with fewer than two waves of tiles (2048->512 @7x7) the dual-M kernel stays ahead (0.0355 vs 0.0397).
+    int pbw = 1, pbh = 1, pbn = 1;
+    choose_patch(g.B, g.Ho, g.Wo, pbw, pbh, pbn);
+    const long deep_tiles = long((g.Wo + pbw - 1) / pbw) * ((g.Ho + pbh - 1) / pbh) * ((g.B + pbn - 1) / pbn) * (g.Cout / kWideN);
+    const bool deep = !(denv2 && denv2[0] == '0') && p.has_out && !p.has_res && !p.has_act && g.Cin >= 512 &&
+                      g.Cout % kWideN == 0 && deep_tiles >= 2L * sm_count();
     if (!(wenv && wenv[0] == '0') && !stem_mode && !p.has_pre && g.kh == 1 && g.kw == 1 && g.pad == 0 && g.Cout % kWideN == 0 &&
-        (p.has_res || (wide_all && (p.has_act || g.Cout > g.Cin)))) {
+        (p.has_res || deep || (wide_all && (p.has_act || g.Cout > g.Cin)))) {
       WideParams& wp = pl->wp;
       std::memset(&wp, 0, sizeof wp);
       pl->wide = 1; pl->kb = 128; pl->block_n = kWideN;
@@ -1822,8 +1834,8 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       const char* penv = std::getenv("B200RN_WIDE_PF");
       wp.pf_dist = penv ? std::max(0, std::min(4, std::atoi(penv))) : 0;   // measured: 2 costs 4 % of the whole step
       const char* senv = std::getenv("B200RN_WIDE_STAGES");
-      wp.stages = senv ? std::max(2, std::min(3, std::atoi(senv))) : 2;
-      const uint32_t fixed = 1024u + 3u * kWideN * 4 + 8u * (2 * 3 + 4 + 32) + 64;
+      wp.stages = senv ? std::max(2, std::min(4, std::atoi(senv))) : ((deep && !p.has_res) ? 4 : 2);
+      const uint32_t fixed = 1024u + (p.has_act ? 3u : 1u) * kWideN * 4 + 8u * (2 * 4 + 4 + 32) + 64;
       const int slots = (int(227u * 1024) - int(fixed)) / int(kChunkBytes) - 3 * wp.stages;   // 16 KB units left for the rings
       const bool use_r = p.has_res || p.has_out;
       if (use_r && p.has_act) { wp.c_slots = std::max(2, slots * 3 / 7); wp.r_slots = slots - wp.c_slots; }

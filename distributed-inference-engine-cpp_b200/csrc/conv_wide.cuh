@@ -63,9 +63,9 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint8_t* r_ring = pipe + S * STAGE_BYTES;
   uint8_t* c_ring = r_ring + (use_r ? SR : 0) * kChunkBytes;
   float* s_bias = reinterpret_cast<float*>(c_ring + (p.has_act ? SC : 0) * kChunkBytes);
-  float* s_scale = s_bias + kWideN;
-  float* s_shift = s_scale + kWideN;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_shift + kWideN);
+  float* s_scale = s_bias + kWideN;                        // scale / shift rows exist only with an activated output
+  float* s_shift = s_scale + (p.has_act ? kWideN : 0);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_shift + (p.has_act ? kWideN : 0));
   uint64_t* full_bar = bars;                 // [S]   operand TMA -> MMA
   uint64_t* empty_bar = full_bar + S;        // [S]   MMA -> operand TMA
   uint64_t* tmem_full = empty_bar + S;       // [2]   MMA -> epilogue
@@ -98,8 +98,10 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * kWideN);
   for (int k = threadIdx.x; k < kWideN; k += blockDim.x) {
     s_bias[k] = __ldg(p.bias + col0 + k);
-    s_scale[k] = p.has_act ? __ldg(p.act_scale + col0 + k) : 1.f;
-    s_shift[k] = p.has_act ? __ldg(p.act_shift + col0 + k) : 0.f;
+    if (p.has_act) {
+      s_scale[k] = __ldg(p.act_scale + col0 + k);
+      s_shift[k] = __ldg(p.act_shift + col0 + k);
+    }
   }
   tc_fence_before();
   __syncthreads();

@@ -204,4 +204,6 @@ CONV_CASES = [
                                                            residual=True, want_out=True, want_act=True)),
     ("wide s2 512->1024 @28 B9 shortcut", dict(B=9, H=28, W=28, Cin=512, Cout=1024, k=1, stride=2, pad=0)),
     ("wide 64->256 @13x9 B3 ragged res raw", dict(B=3, H=13, W=9, Cin=64, Cout=256, k=1, stride=1, pad=0, residual=True)),
+    # large-K plain 1x1 conv with at least two waves of tiles: the wide kernel's four-stage configuration
+    ("deep 512->256 @28 B50 (306 tiles)", dict(B=50, H=28, W=28, Cin=512, Cout=256, k=1, stride=1, pad=0, relu=1)),
 ]
