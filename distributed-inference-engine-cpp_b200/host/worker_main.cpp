@@ -54,8 +54,10 @@ int main(int argc, char** argv) {
   mini_http::Server server;
   server.Post("/infer", [&worker](const mini_http::Request& req, mini_http::Response& res) {
     try {
-      auto request = json::parse(req.body);
-      res.set_content(worker.handleInfer(request).dump(), "application/json");
+      // B200RN_FAST_JSON=0 forces the reference's parse-then-convert path for every body (A/B and tests)
+      static const bool fast = !(std::getenv("B200RN_FAST_JSON") && std::getenv("B200RN_FAST_JSON")[0] == '0');
+      if (fast) res.set_content(worker.handleInferBody(req.body).dump(), "application/json");
+      else res.set_content(worker.handleInfer(json::parse(req.body)).dump(), "application/json");
     } catch (const std::exception& e) {
       json error;
       error["error"] = e.what();

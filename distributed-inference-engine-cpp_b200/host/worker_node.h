@@ -24,6 +24,7 @@
 #include <nlohmann/json.hpp>
 
 #include "batch_processor.h"
+#include "fast_request.h"
 #include "lru_cache.h"
 
 struct InferenceRequest {
@@ -54,6 +55,18 @@ class WorkerNodeT {
   }
   ~WorkerNodeT() { batcher_.stop(); }
 
+  // Raw-body entry: the common request shape is scanned straight into a vector<float> (fast_request.h); every
+  // other body takes the nlohmann path below, so what is accepted and every error text stay the same.
+  json handleInferBody(const std::string& body) {
+    std::string request_id;
+    std::vector<float> input_data;
+    if (fast_request::parse(body, request_id, input_data)) {
+      ++total_requests_;
+      return handleInferFields(request_id, input_data);
+    }
+    return handleInfer(json::parse(body));
+  }
+
   json handleInfer(const json& request) {
     ++total_requests_;
     // A missing key reads as null and the conversion then throws nlohmann's type_error.302
@@ -66,7 +79,12 @@ class WorkerNodeT {
     };
     std::string request_id = field("request_id");
     std::vector<float> input_data = field("input_data");
+    return handleInferFields(request_id, input_data);
+  }
 
+  // The handler after its two fields have been read (by the conversions above, or by fast_request::parse from the
+  // raw body); the caller has counted the request.
+  json handleInferFields(const std::string& request_id, const std::vector<float>& input_data) {
     if (auto hit = cache_.get(input_data)) {
       ++cache_hits_;
       json response;

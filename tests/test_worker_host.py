@@ -83,3 +83,96 @@ def test_large_body_and_keep_alive(worker):
     assert r.status_code == 200 and r.json()["output_data"][1] == 150528.0
     r = s.post(worker + "/infer", json={"request_id": "big2", "input_data": x}, timeout=30)
     assert r.json()["cached"] is True
+
+
+# ---- the fast request scanner must be indistinguishable from the nlohmann path ---------------------------------
+
+@pytest.fixture(scope="module")
+def worker_pair():
+    """Two stub workers: the default one (fast scanner first) and one forced onto the parse-then-convert path."""
+    if not os.path.exists(FAKE):
+        pytest.skip("worker_node_fake not built (nlohmann/json.hpp not found)")
+    procs, urls = [], []
+    for fast in ("1", "0"):
+        port = _free_port()
+        procs.append(subprocess.Popen([FAKE, str(port), "w", "unused.onnx"], env=dict(os.environ, B200RN_FAST_JSON=fast),
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+        urls.append("http://127.0.0.1:%d" % port)
+    for u in urls:
+        for _ in range(100):
+            try:
+                requests.get(u + "/health", timeout=0.5)
+                break
+            except Exception:
+                time.sleep(0.05)
+    yield urls
+    for p in procs:
+        p.terminate()
+        p.wait(timeout=5)
+
+
+FAST_JSON_BODIES = [
+    '{"request_id":"a","input_data":[1,2,3]}',
+    '{ "input_data" : [ 1.5 , -2e3 , 0.1 , 1E-2 , 3.0e+1 ] , "request_id" : "key order and spaces" }',
+    '{"request_id":"ints","input_data":[-0,0,7,-7,16777217,123456789012345678]}',          # int64 route, -0 -> +0
+    '{"request_id":"big ints","input_data":[1234567890123456789,18446744073709551615,123456789012345678901234567890]}',
+    '{"request_id":"denormals and limits","input_data":[1e-45,1.4e-45,3.4028235e38,3.5e38,1e-320,2.2250738585072014e-308]}',
+    '{"request_id":"rounding","input_data":[0.1,0.2,0.30000000000000004,16777216.5,16777217.5,1.0000000596046448]}',
+    '{"request_id":"empty","input_data":[]}',
+    '{"request_id":"esc\\u0041ped","input_data":[1]}',
+    '{"request_id":"caf\\u00e9 \xc3\xa9","input_data":[1]}',
+    '{"request_id":"x","input_data":[1],"extra":true}',
+    '{"request_id":"x","request_id":"dup","input_data":[1]}',
+    '{"request_id":"x","input_data":[1,"2"]}',
+    '{"request_id":"x","input_data":[1,null]}',
+    '{"request_id":"x","input_data":[true]}',
+    '{"request_id":"x","input_data":[01]}',
+    '{"request_id":"x","input_data":[1.]}',
+    '{"request_id":"x","input_data":[.5]}',
+    '{"request_id":"x","input_data":[+1]}',
+    '{"request_id":"x","input_data":[1e999]}',
+    '{"request_id":"x","input_data":[NaN]}',
+    '{"request_id":"x","input_data":[1,]}',
+    '{"request_id":"x","input_data":[1] }  trailing',
+    '{"request_id":"x","input_data":{"a":1}}',
+    '{"request_id":7,"input_data":[1]}',
+    '{"input_data":[1]}',
+    '{"request_id":"x"}',
+    '[1,2]',
+    '',
+    '{"request_id":"x","input_data":[1]',
+]
+
+
+@pytest.mark.parametrize("body", FAST_JSON_BODIES)
+def test_fast_scanner_equals_nlohmann_path(worker_pair, body):
+    fast, slow = worker_pair
+    a = requests.post(fast + "/infer", data=body.encode("utf-8"), timeout=5)
+    b = requests.post(slow + "/infer", data=body.encode("utf-8"), timeout=5)
+    assert a.status_code == b.status_code
+
+    def norm(t):                      # only the measured time may differ between two processes
+        import re
+        return re.sub(r'"inference_time_us":\d+', '"inference_time_us":0', t)
+    assert norm(a.text) == norm(b.text)
+
+
+def test_fast_scanner_random_numbers(worker_pair):
+    import random
+    fast, slow = worker_pair
+    rnd = random.Random(5)
+    for trial in range(30):
+        vals = []
+        for _ in range(rnd.randint(1, 40)):
+            kind = rnd.random()
+            if kind < 0.3:
+                vals.append(str(rnd.randint(-10**rnd.randint(1, 17), 10**rnd.randint(1, 17))))
+            elif kind < 0.7:
+                vals.append(repr(rnd.uniform(-1e3, 1e3)))
+            else:
+                vals.append("%.*e" % (rnd.randint(0, 17), rnd.uniform(-1, 1) * 10.0 ** rnd.randint(-50, 39)))
+        body = '{"request_id":"t%d","input_data":[%s]}' % (trial, ",".join(vals))
+        a = requests.post(fast + "/infer", data=body, timeout=5).json()
+        b = requests.post(slow + "/infer", data=body, timeout=5).json()
+        a.pop("inference_time_us", None), b.pop("inference_time_us", None)
+        assert a == b, body

@@ -2,7 +2,11 @@
 """Closed-loop load on one worker_node over HTTP, in the manner of the reference's benchmark.py
 (threads x requests, request_id "req_{i}", percentiles by sorted index int(n*p): benchmark.py:49-52,113-116),
 once with its native 3-float payload (cache path) and once with full 3x224x224 payloads, unique per request
-(inference path).  Prints one JSON object.   usage: serve_bench.py [--requests N] [--threads T] [--mode fp16]"""
+(inference path).  Prints one JSON object.
+   usage: serve_bench.py [--requests N] [--threads T] [--mode fp16] [--workers W] [--gateway]
+--workers W starts W worker_node processes, worker i on GPU i % (number of GPUs); --gateway puts the gateway in
+front of them and sends every request there (BASELINE configs[2]: gateway + 3 workers, 50 client threads); without
+--gateway only the first worker is loaded."""
 import argparse
 import json
 import os
@@ -53,19 +57,52 @@ def main():
     ap.add_argument("--requests", type=int, default=640)
     ap.add_argument("--threads", type=int, default=32)
     ap.add_argument("--mode", default="fp16")
+    ap.add_argument("--workers", type=int, default=1)
+    ap.add_argument("--gateway", action="store_true")
     a = ap.parse_args()
-    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
-    env = dict(os.environ, B200RN_MODE=a.mode, B200RN_MAX_BATCH="32")
-    proc = subprocess.Popen([os.path.join(b200rn_loader.PKG_DIR, "worker_node"), str(port), "worker_1", bench.model_path()],
-                            env=env, stdout=subprocess.DEVNULL, stderr=subprocess.STDOUT)
-    url = "http://127.0.0.1:%d" % port
+    a_workers = max(1, a.workers)
+    import torch
+    ngpu = max(1, torch.cuda.device_count())
+
+    def free_port():
+        s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+        return p
+
+    procs, addrs = [], []
+    for i in range(a_workers):
+        port = free_port()
+        env = dict(os.environ, B200RN_MODE=a.mode, B200RN_MAX_BATCH="32", B200RN_DEVICE=str(i % ngpu))
+        procs.append(subprocess.Popen([os.path.join(b200rn_loader.PKG_DIR, "worker_node"), str(port), "worker_%d" % (i + 1),
+                                       bench.model_path()], env=env, stdout=subprocess.DEVNULL, stderr=subprocess.STDOUT))
+        addrs.append("127.0.0.1:%d" % port)
+    url = "http://" + addrs[0]
+    proc = procs[0]
     try:
-        for _ in range(1200):
-            try:
-                requests.get(url + "/health", timeout=0.5)
-                break
-            except Exception:
-                time.sleep(0.1)
+        for ad in addrs:
+            for _ in range(1200):
+                try:
+                    requests.get("http://" + ad + "/health", timeout=0.5)
+                    break
+                except Exception:
+                    time.sleep(0.1)
+        if a.gateway:
+            gport = free_port()
+            procs.append(subprocess.Popen([os.path.join(b200rn_loader.PKG_DIR, "gateway")] + addrs,
+                                          env=dict(os.environ, GATEWAY_PORT=str(gport)), stdout=subprocess.DEVNULL,
+                                          stderr=subprocess.STDOUT))
+            url = "http://127.0.0.1:%d" % gport
+            for _ in range(200):
+                try:
+                    requests.get(url + "/stats", timeout=0.5)
+                    break
+                except Exception:
+                    time.sleep(0.05)
+        # untimed warm-up: the first batches of a worker build its per-batch-size launch plans
+        for ad in addrs:
+            for k in range(4):
+                w = np.full(150528, 1000.0 + k, dtype=np.float32)
+                requests.post("http://" + ad + "/infer", data=json.dumps({"request_id": "warm_%d" % k, "input_data": w.tolist()}),
+                              timeout=120)
         small = [json.dumps({"request_id": "req_%d" % i, "input_data": [float(i % 10), float(i % 10 + 1), float(i % 10 + 2)]})
                  for i in range(a.requests * 4)]
         out = {"cache_path_3_floats": run(url, small, a.threads)}
@@ -78,11 +115,16 @@ def main():
             big.append(json.dumps({"request_id": "req_%d" % i, "input_data": x.tolist()}))
         out["payload_bytes"] = len(big[0])
         out["inference_path_150528_floats"] = run(url, big, a.threads)
-        out["health"] = requests.get(url + "/health", timeout=5).json()
+        out["config"] = {"workers": a_workers, "gpus": ngpu, "gateway": bool(a.gateway), "threads": a.threads, "mode": a.mode}
+        out["health"] = [requests.get("http://" + ad + "/health", timeout=5).json() for ad in addrs]
+        if a.gateway:
+            out["stats"] = requests.get(url + "/stats", timeout=5).json()
         print(json.dumps(out))
     finally:
-        proc.terminate()
-        proc.wait(timeout=10)
+        for pr in procs:
+            pr.terminate()
+        for pr in procs:
+            pr.wait(timeout=10)
 
 
 if __name__ == "__main__":
