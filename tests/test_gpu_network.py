@@ -201,6 +201,23 @@ def test_double_buffered_submit(tmp_path):
     eng.close()
 
 
+def test_graph_replay_equals_eager(tmp_path):
+    """The engine runs a (batch, slot) combination eagerly the first time, captures a CUDA graph the second time and
+    replays it afterwards: all three must give the same bits for the same data, per batch size, with other batch
+    sizes and other data in between."""
+    p = str(tmp_path / "s.onnx")
+    gen.write_model(p, "small64", seed=6)
+    eng = pkg.Engine(p, mode="fp16", max_batch=8)
+    rs = np.random.RandomState(3)
+    data = {b: [rs.randn(b, 3, 64, 64).astype(np.float32) for _ in range(2)] for b in (1, 3, 8)}
+    first = {b: [eng.infer_packed(x) for x in xs] for b, xs in data.items()}          # eager, then capture
+    for _ in range(3):                                                                 # replays, interleaved
+        for b in (8, 1, 3):
+            for x, w in zip(data[b], first[b]):
+                assert np.array_equal(eng.infer_packed(x), w)
+    eng.close()
+
+
 def test_softmax_graph_and_generic_fallback_layers(tmp_path):
     """A graph ending in Softmax (not in the v2-7 file) runs, and changes results exactly as the op says."""
     p = str(tmp_path / "sm.onnx")
