@@ -124,6 +124,8 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
   const int my_tiles = (p.total_tiles - int(blockIdx.x) + int(gridDim.x) - 1) / int(gridDim.x);   // >= 1: grid <= tiles
 
   if (warp == 0) {

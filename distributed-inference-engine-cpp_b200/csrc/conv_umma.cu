@@ -25,6 +25,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "kernels.h"
@@ -95,6 +96,14 @@ __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarr
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// Programmatic dependent launch: every tcgen05 kernel is launched with programmaticStreamSerializationAllowed, lets
+// its successor be scheduled at once (launch_dependents) and only then waits for its predecessor's memory
+// (griddepcontrol.wait).  Barrier init, TMEM allocation, descriptor prefetch and the parameter loads of kernel N+1
+// thus run while kernel N's last CTAs are still finishing.  Everything that reads or WRITES an activation buffer
+// comes after the wait: the arena reuses a dead tensor's memory for the next layer's output.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait_prior_grid() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
@@ -353,6 +362,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -657,6 +668,8 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
 
   auto tile_coord = [&](int tile, int& x0, int& y0, int& n, int& col0) {
     const int nt = tile % p.n_tiles;
@@ -923,6 +936,8 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
 
   auto tile_coord = [&](int i, int& x0, int& y0, int& n) {
     int mt = (int(blockIdx.x) + i * int(gridDim.x)) / p.n_tiles;
@@ -1082,6 +1097,8 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
 
   // M tile index -> patch origin; an index past the last tile lands beyond the batch, where TMA loads read
   // zeros and TMA stores are clipped
@@ -1478,6 +1495,26 @@ static void plan_geometry(UmmaConvPlan& pl) {
   pl.smem_bytes = fixed + uint32_t(stages) * stage_eff;
 }
 
+static bool pdl_enabled() {
+  static const bool on = !(std::getenv("B200RN_PDL") && std::getenv("B200RN_PDL")[0] == '0');
+  return on;
+}
+
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kern)(KArgs...), int grid, int block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(unsigned(grid));
+  cfg.blockDim = dim3(unsigned(block));
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 template <typename T, int BLOCK_N, int KB, int EPI>
 static cudaError_t launch_inst(const UmmaConvPlan* pl, cudaStream_t s) {
   auto kern = conv_umma_kernel<T, BLOCK_N, KB, EPI>;
@@ -1490,8 +1527,7 @@ static cudaError_t launch_inst(const UmmaConvPlan* pl, cudaStream_t s) {
     configured_device = dev;
   }
   // the four operand-transform warps exist only for layers that need them
-  kern<<<pl->grid, pl->p.has_pre ? kThreads : kBaseThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->p);
-  return cudaGetLastError();
+  return launch_pdl(kern, pl->grid, pl->p.has_pre ? kThreads : kBaseThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->p);
 }
 
 template <typename T, int BLOCK_N, int KB>
@@ -1520,8 +1556,7 @@ static cudaError_t launch_halo(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  kern<<<pl->grid, kBaseThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmOut, pl->hp);
-  return cudaGetLastError();
+  return launch_pdl(kern, pl->grid, kBaseThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmOut, pl->hp);
 }
 
 template <typename T>
@@ -1535,8 +1570,7 @@ static cudaError_t launch_stem2(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  kern<<<pl->grid, kBaseThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmOut, pl->sp);
-  return cudaGetLastError();
+  return launch_pdl(kern, pl->grid, kBaseThreads, pl->smem_bytes, s, pl->tmA, pl->tmOut, pl->sp);
 }
 
 template <typename T, int BLOCK_N>
@@ -1550,8 +1584,7 @@ static cudaError_t launch_dual(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  kern<<<pl->grid, kBaseThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmOut, pl->dp);
-  return cudaGetLastError();
+  return launch_pdl(kern, pl->grid, kBaseThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmOut, pl->dp);
 }
 
 template <typename T, int N1>
@@ -1565,8 +1598,7 @@ static cudaError_t launch_tail(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  kern<<<pl->grid, kTailThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmW1, pl->tmRes, pl->tmOut, pl->tmOut1, pl->tp);
-  return cudaGetLastError();
+  return launch_pdl(kern, pl->grid, kTailThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmW1, pl->tmRes, pl->tmOut, pl->tmOut1, pl->tp);
 }
 
 template <typename T>
@@ -1580,8 +1612,7 @@ static cudaError_t launch_wide(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  kern<<<pl->grid, kWideThreads, pl->smem_bytes, s>>>(pl->tmA, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->wp);
-  return cudaGetLastError();
+  return launch_pdl(kern, pl->grid, kWideThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->wp);
 }
 
 cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {

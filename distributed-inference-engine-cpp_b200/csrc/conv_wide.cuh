@@ -107,6 +107,8 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
 
   if (warp == 0) {
     // ===== operand TMA producer =====
