@@ -1601,9 +1601,9 @@ static cudaError_t launch_tail(const UmmaConvPlan* pl, cudaStream_t s) {
   return launch_pdl(kern, pl->grid, kTailThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmW1, pl->tmRes, pl->tmOut, pl->tmOut1, pl->tp);
 }
 
-template <typename T>
+template <typename T, int N>
 static cudaError_t launch_wide(const UmmaConvPlan* pl, cudaStream_t s) {
-  auto kern = conv_wide_kernel<T>;
+  auto kern = conv_wide_kernel<T, N>;
   static thread_local int configured_device = -1;
   int dev = 0;
   cudaGetDevice(&dev);
@@ -1617,7 +1617,10 @@ static cudaError_t launch_wide(const UmmaConvPlan* pl, cudaStream_t s) {
 
 cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
   const bool bf = pl->dt == DType::BF16;
-  if (pl->wide) return bf ? launch_wide<__nv_bfloat16>(pl, s) : launch_wide<__half>(pl, s);
+  if (pl->wide) {
+    if (pl->block_n == 128) return bf ? launch_wide<__nv_bfloat16, 128>(pl, s) : launch_wide<__half, 128>(pl, s);
+    return bf ? launch_wide<__nv_bfloat16, 256>(pl, s) : launch_wide<__half, 256>(pl, s);
+  }
   if (pl->tail) {
     if (pl->tp_n1 == 64) return bf ? launch_tail<__nv_bfloat16, 64>(pl, s) : launch_tail<__half, 64>(pl, s);
     return bf ? launch_tail<__nv_bfloat16, 128>(pl, s) : launch_tail<__half, 128>(pl, s);
@@ -1847,14 +1850,13 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
         (p.has_res || deep || (wide_all && (p.has_act || g.Cout > g.Cin)))) {
       WideParams& wp = pl->wp;
       std::memset(&wp, 0, sizeof wp);
-      pl->wide = 1; pl->kb = 128; pl->block_n = kWideN;
+      pl->wide = 1; pl->kb = 128;
       int bw = 1, bh = 1, bn = 1;
       choose_patch(g.B, g.Ho, g.Wo, bw, bh, bn);
       wp.cblks = g.Cin / 64; wp.num_k_iters = wp.cblks; wp.kw = 1; wp.stride = g.stride; wp.pad = 0;
       wp.bw = bw; wp.bh = bh; wp.bn = bn;
       wp.tiles_w = (g.Wo + bw - 1) / bw; wp.tiles_h = (g.Ho + bh - 1) / bh;
       wp.m_tiles = wp.tiles_w * wp.tiles_h * ((g.B + bn - 1) / bn);
-      wp.n_tiles = g.Cout / kWideN;
       wp.has_res = p.has_res; wp.has_out = p.has_out; wp.has_act = p.has_act; wp.relu = p.relu; wp.act_relu = p.act_relu;
       wp.rows = uint32_t(bw * bh * bn); wp.a_bytes = wp.rows * 128u;
       wp.bias = e.bias; wp.act_scale = e.act_scale; wp.act_shift = e.act_shift;
@@ -1864,27 +1866,44 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       }
       const char* penv = std::getenv("B200RN_WIDE_PF");
       wp.pf_dist = penv ? std::max(0, std::min(4, std::atoi(penv))) : 0;   // measured: 2 costs 4 % of the whole step
+      // Stationary weights: the CTA keeps one N tile, so when that tile's whole slab (N x Cin) fits beside the staging
+      // rings it is loaded once and only A streams -- the operand ring was what bounded the raw + activated layers
+      // (two 48 KB stages, B re-fetched for every tile).  Cin <= 128: N = 256 (slab <= 64 KB); Cin = 256: N = 128
+      // (64 KB) with four A stages = one tile ahead; larger Cin streams both operands as before.
+      const char* benv = std::getenv("B200RN_WIDE_BSTAT");
+      const bool bstat_ok = !(benv && benv[0] == '0') && !deep;
+      int N = kWideN;
+      wp.b_stationary = 0;
+      if (bstat_ok && g.Cin <= 128) wp.b_stationary = 1;
+      else if (bstat_ok && g.Cin == 256 && g.Cout % 128 == 0) { wp.b_stationary = 1; N = 128; }
+      pl->block_n = N;
+      wp.n_tiles = g.Cout / N;
       const char* senv = std::getenv("B200RN_WIDE_STAGES");
-      wp.stages = senv ? std::max(2, std::min(4, std::atoi(senv))) : ((deep && !p.has_res) ? 4 : 2);
-      const uint32_t fixed = 1024u + (p.has_act ? 3u : 1u) * kWideN * 4 + 8u * (2 * 4 + 4 + 32) + 64;
-      const int slots = (int(227u * 1024) - int(fixed)) / int(kChunkBytes) - 3 * wp.stages;   // 16 KB units left for the rings
+      const uint32_t slab = wp.b_stationary ? uint32_t(wp.num_k_iters) * uint32_t(N) * 128u : 0u;
+      const uint32_t stage_bytes = wp.b_stationary ? uint32_t(kTileM) * 128u : uint32_t(kTileM + N) * 128u;
+      wp.stages = senv ? std::max(2, std::min(4, std::atoi(senv)))
+                       : (wp.b_stationary ? std::max(2, std::min(4, wp.num_k_iters + 1)) : ((deep && !p.has_res) ? 4 : 2));
+      const uint32_t fixed = 1024u + (p.has_act ? 3u : 1u) * uint32_t(N) * 4 + 8u * (2 * 4 + 4 + 33) + 64;
+      const int slots = (int(227u * 1024) - int(fixed) - int(slab) - int(uint32_t(wp.stages) * stage_bytes)) / int(kChunkBytes);
       const bool use_r = p.has_res || p.has_out;
       if (use_r && p.has_act) { wp.c_slots = std::max(2, slots * 3 / 7); wp.r_slots = slots - wp.c_slots; }
       else if (use_r) wp.r_slots = slots;
       else wp.c_slots = slots;
       wp.r_slots = std::min(8, wp.r_slots); wp.c_slots = std::min(8, wp.c_slots);
+      if ((use_r && wp.r_slots < 2) || (p.has_act && wp.c_slots < 2)) { delete pl; return failmsg("wide-epilogue conv: shared memory does not hold the staging rings"); }
       const int sms = sm_count();
       const long total = long(wp.m_tiles) * wp.n_tiles;
       int grid = int(std::min<long>(total, sms));
       grid = std::max(wp.n_tiles, (grid / wp.n_tiles) * wp.n_tiles);
       pl->grid = grid;
-      pl->smem_bytes = fixed + uint32_t(3 * wp.stages + (use_r ? wp.r_slots : 0) + (p.has_act ? wp.c_slots : 0)) * kChunkBytes;
+      pl->smem_bytes = fixed + slab + uint32_t(wp.stages) * stage_bytes +
+                       uint32_t((use_r ? wp.r_slots : 0) + (p.has_act ? wp.c_slots : 0)) * kChunkBytes;
       std::string wmsg;
       bool wok = encode_act(&pl->tmA, dt, in, g.B, g.H, g.W, g.Cin, bw, bh, bn, g.stride, wmsg);
       if (wok) {
         uint64_t wd[2] = {uint64_t(g.Cin), uint64_t(g.Cout)};
         uint64_t ws[1] = {uint64_t(g.Cin) * 2};
-        uint32_t wb[2] = {64, uint32_t(kWideN)};
+        uint32_t wb[2] = {64, uint32_t(N)};
         uint32_t we[2] = {1, 1};
         wok = encode(&pl->tmW, dt, 2, w_packed, wd, ws, wb, we, false, wmsg);
       }
@@ -1894,9 +1913,9 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       if (wok) wok = encode_act(&pl->tmRes, dt, e.residual ? e.residual : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, wmsg);
       if (!wok) { delete pl; return failmsg(wmsg); }
       if (std::getenv("B200RN_VERBOSE"))
-        std::fprintf(stderr, "[b200rn] conv 1x1 s%d %d->%d @%dx%d B%d: wide-epilogue patch=%dx%dx%d m_tiles=%d n_tiles=%d grid=%d stages=%d r_slots=%d c_slots=%d smem=%u\n",
-                     g.stride, g.Cin, g.Cout, g.H, g.W, g.B, bw, bh, bn, wp.m_tiles, wp.n_tiles, grid, wp.stages, wp.r_slots, wp.c_slots,
-                     pl->smem_bytes);
+        std::fprintf(stderr, "[b200rn] conv 1x1 s%d %d->%d @%dx%d B%d: wide-epilogue N=%d bstat=%d patch=%dx%dx%d m_tiles=%d n_tiles=%d grid=%d stages=%d r_slots=%d c_slots=%d smem=%u\n",
+                     g.stride, g.Cin, g.Cout, g.H, g.W, g.B, N, wp.b_stationary, bw, bh, bn, wp.m_tiles, wp.n_tiles, grid, wp.stages,
+                     wp.r_slots, wp.c_slots, pl->smem_bytes);
       return pl;
     }
   }

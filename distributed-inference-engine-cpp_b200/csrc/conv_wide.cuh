@@ -25,7 +25,7 @@ constexpr int kWideThreads = (4 + kWideEpiWarps) * 32;   // operand TMA, MMA, st
 struct WideParams {
   int num_k_iters, cblks, kw, stride, pad;
   int bw, bh, bn, tiles_w, tiles_h, m_tiles, n_tiles;
-  int stages, r_slots, c_slots;
+  int stages, r_slots, c_slots, b_stationary;
   int has_res, has_out, has_act, relu, act_relu;
   int pf_dist;                 // residual L2 prefetch distance in tiles (0 = off)
   uint32_t rows, a_bytes;
@@ -44,28 +44,30 @@ __device__ __forceinline__ WideTile wide_decode(const WideParams& p, int mt) {
   return t;
 }
 
-template <typename T>
+template <typename T, int N>
 __global__ void __launch_bounds__(kWideThreads, 1)
 conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
                  const __grid_constant__ CUtensorMap tmAct, const WideParams p) {
-  constexpr int kChunks = kWideN / 64;
+  constexpr int kChunks = N / 64;
   constexpr uint32_t A_BYTES = kTileM * 128;
-  constexpr uint32_t B_BYTES = kWideN * 128;
-  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr uint32_t B_BYTES = N * 128;
+  // a stage holds an A tile and, unless the CTA's weight slab is stationary, the matching B tile
+  const uint32_t STAGE_BYTES = p.b_stationary ? A_BYTES : A_BYTES + B_BYTES;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int S = p.stages, SR = p.r_slots, SC = p.c_slots;
   const bool use_r = p.has_res || p.has_out;      // the raw / residual ring exists
   const int SS = use_r ? SR : SC;                 // "chunk staged" barriers
-  uint8_t* pipe = smem;
+  uint8_t* bstat = smem;                          // [num_k_iters x B tile] when b_stationary
+  uint8_t* pipe = bstat + (p.b_stationary ? p.num_k_iters * B_BYTES : 0);
   uint8_t* r_ring = pipe + S * STAGE_BYTES;
   uint8_t* c_ring = r_ring + (use_r ? SR : 0) * kChunkBytes;
   float* s_bias = reinterpret_cast<float*>(c_ring + (p.has_act ? SC : 0) * kChunkBytes);
-  float* s_scale = s_bias + kWideN;                        // scale / shift rows exist only with an activated output
-  float* s_shift = s_scale + (p.has_act ? kWideN : 0);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_shift + (p.has_act ? kWideN : 0));
+  float* s_scale = s_bias + N;                             // scale / shift rows exist only with an activated output
+  float* s_shift = s_scale + (p.has_act ? N : 0);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_shift + (p.has_act ? N : 0));
   uint64_t* full_bar = bars;                 // [S]   operand TMA -> MMA
   uint64_t* empty_bar = full_bar + S;        // [S]   MMA -> operand TMA
   uint64_t* tmem_full = empty_bar + S;       // [2]   MMA -> epilogue
@@ -74,11 +76,12 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* r_empty = r_full + 8;            // [SR]  store warp -> residual TMA
   uint64_t* c_free = r_empty + 8;            // [SC]  store warp -> epilogue (activated-copy slot reusable)
   uint64_t* staged = c_free + 8;             // [SS]  epilogue -> store warp (8 warp arrivals: the owning group)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(staged + 8);
+  uint64_t* bstat_bar = staged + 8;          // [1]   stationary weights landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bstat_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_tile = int(blockIdx.x) % p.n_tiles;
-  const int col0 = n_tile * kWideN;
+  const int col0 = n_tile * N;
   const int m_first = int(blockIdx.x) / p.n_tiles, m_step = int(gridDim.x) / p.n_tiles;
   const int my_tiles = m_first < p.m_tiles ? (p.m_tiles - m_first + m_step - 1) / m_step : 0;
 
@@ -93,10 +96,11 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_init(smem_u32(&r_full[i]), 1); mbar_init(smem_u32(&r_empty[i]), 1);
       mbar_init(smem_u32(&c_free[i]), 1); mbar_init(smem_u32(&staged[i]), kWideGroupWarps);
     }
+    mbar_init(smem_u32(bstat_bar), 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * kWideN);
-  for (int k = threadIdx.x; k < kWideN; k += blockDim.x) {
+  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * N);
+  for (int k = threadIdx.x; k < N; k += blockDim.x) {
     s_bias[k] = __ldg(p.bias + col0 + k);
     if (p.has_act) {
       s_scale[k] = __ldg(p.act_scale + col0 + k);
@@ -115,29 +119,36 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      if (p.b_stationary && my_tiles > 0) {      // the CTA's N tile never changes: fetch its weights once
+        const uint32_t bb = smem_u32(bstat_bar);
+        mbar_expect_tx(bb, uint32_t(p.num_k_iters) * B_BYTES);
+        for (int it = 0; it < p.num_k_iters; ++it) tma_load_2d(smem_u32(bstat + it * B_BYTES), &tmW, bb, it * 64, col0);
+      }
       for (int i = 0; i < my_tiles; ++i) {
         const WideTile tc = wide_decode(p, m_first + i * m_step);
         for (int it = 0; it < p.num_k_iters; ++it) {
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
           const uint32_t fb = smem_u32(&full_bar[stage]);
-          mbar_expect_tx(fb, p.a_bytes + B_BYTES);
+          mbar_expect_tx(fb, p.b_stationary ? p.a_bytes : p.a_bytes + B_BYTES);
           const uint32_t a_dst = smem_u32(pipe + stage * STAGE_BYTES);
           const int tap = it / p.cblks, cb = it - tap * p.cblks;
           const int ky = tap / p.kw, kx = tap - ky * p.kw;
           tma_load_4d(a_dst, &tmA, fb, cb * 64, tc.w0 * p.stride - p.pad + kx, tc.h0 * p.stride - p.pad + ky, tc.n0);
-          tma_load_2d(a_dst + A_BYTES, &tmW, fb, it * 64, col0);
+          if (!p.b_stationary) tma_load_2d(a_dst + A_BYTES, &tmW, fb, it * 64, col0);
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer (one thread) =====
-    constexpr uint32_t idesc = make_idesc<T, kWideN>();
+    constexpr uint32_t idesc = make_idesc<T, N>();
     constexpr uint32_t desc_hi = smem_desc_hi<128>();
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t pipe_lo = smem_desc_lo(smem_u32(pipe));
+      const uint32_t bstat_lo = smem_desc_lo(smem_u32(bstat));
+      if (p.b_stationary && my_tiles > 0) mbar_wait(smem_u32(bstat_bar), 0);
       for (int i = 0; i < my_tiles; ++i) {
         const int buf = i & 1;
         const bool tr = p.trace && blockIdx.x == 0 && i < 32;
@@ -145,13 +156,13 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(smem_u32(&tmem_empty[buf]), ((uint32_t(i) >> 1) & 1) ^ 1);   // epilogue drained this accumulator
         tc_fence_after();
         if (tr) p.trace[i * 8 + 1] = clock64();
-        const uint32_t tmem_d = tmem_base + uint32_t(buf * kWideN);
+        const uint32_t tmem_d = tmem_base + uint32_t(buf * N);
         for (int it = 0; it < p.num_k_iters; ++it) {
           mbar_wait(smem_u32(&full_bar[stage]), phase);
           tc_fence_after();
           if (tr && it < 5) p.trace[i * 8 + 2 + it] = clock64();
           const uint32_t a_lo = pipe_lo + uint32_t(stage) * (STAGE_BYTES >> 4);
-          const uint32_t b_lo = a_lo + (A_BYTES >> 4);
+          const uint32_t b_lo = p.b_stationary ? bstat_lo + uint32_t(it) * (B_BYTES >> 4) : a_lo + (A_BYTES >> 4);
 #pragma unroll
           for (int k = 0; k < 4; ++k) umma_f16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (it | k) != 0 ? 1u : 0u);
           umma_commit(smem_u32(&empty_bar[stage]));
@@ -244,7 +255,7 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tc_fence_after();
         if (tr) trc[1] = clock64();
         uint32_t acc[32];
-        tmem_ld_32x32b_x32(lane_addr + uint32_t(buf * kWideN + c * 64 + g * 32), acc);
+        tmem_ld_32x32b_x32(lane_addr + uint32_t(buf * N + c * 64 + g * 32), acc);
         const uint32_t raw_row = smem_u32(r_ring + slot * kChunkBytes) + row_off;
         const uint32_t act_row = smem_u32(c_ring + cslot * kChunkBytes) + row_off;
         const uint32_t pcol = uint32_t(c * 64 + g * 32) * 4;       // byte offset of this thread's first channel in the parameter rows
@@ -303,5 +314,5 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 2 * kWideN);
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * N);
 }
