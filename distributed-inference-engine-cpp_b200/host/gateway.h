@@ -62,14 +62,22 @@ class Gateway {
   static std::string extractRequestId(const std::string& body);
 
   // Forwards `body` and returns the answering worker's response body.
-  std::string route(const std::string& body) {
-    const std::string request_id = extractRequestId(body);
+  std::string route(const std::string& body) { return routeAs(extractRequestId(body), body, "application/json", ""); }
+
+  // The octet-stream side channel (raw float32 sample, id in X-Request-Id): same placement and fail-over, the
+  // header travels with the body.
+  std::string routeRaw(const std::string& request_id, const std::string& body) {
+    return routeAs(request_id, body, "application/octet-stream", "X-Request-Id: " + request_id + "\r\n");
+  }
+
+  std::string routeAs(const std::string& request_id, const std::string& body, const std::string& content_type,
+                      const std::string& extra_headers) {
     const std::string target = ring_.getNode(request_id);
     if (target.empty()) throw std::runtime_error("No workers available");
-    if (auto r = tryNode(target, body)) return *r;
+    if (auto r = tryNode(target, body, content_type, extra_headers)) return *r;
     for (const auto& node : ring_.getAllNodes())
       if (node != target)
-        if (auto r = tryNode(node, body)) return *r;
+        if (auto r = tryNode(node, body, content_type, extra_headers)) return *r;
     throw std::runtime_error("All workers failed or circuit breakers open");
   }
 
@@ -92,13 +100,14 @@ class Gateway {
   std::string nodeFor(const std::string& request_id) const { return ring_.getNode(request_id); }
 
  private:
-  std::optional<std::string> tryNode(const std::string& node, const std::string& body) {
+  std::optional<std::string> tryNode(const std::string& node, const std::string& body, const std::string& content_type,
+                                     const std::string& extra_headers) {
     auto b = breakers_.find(node);
     if (b == breakers_.end()) return std::nullopt;
     if (!b->second->allowRequest()) return std::nullopt;
     auto c = clients_.find(node);
     if (c == clients_.end()) { b->second->recordFailure(); return std::nullopt; }
-    mini_http::ClientResult r = c->second->Post("/infer", body, "application/json");
+    mini_http::ClientResult r = c->second->Post("/infer", body, content_type, extra_headers);
     if (r.ok && r.status == 200 && json::accept(r.body)) {
       b->second->recordSuccess();
       return std::move(r.body);

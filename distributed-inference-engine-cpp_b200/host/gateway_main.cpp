@@ -29,6 +29,14 @@ int main(int argc, char** argv) {
   mini_http::Server server;
   server.Post("/infer", [&gateway](const mini_http::Request& req, mini_http::Response& res) {
     try {
+      auto ct = req.headers.find("content-type");
+      if (ct != req.headers.end() && ct->second.compare(0, 24, "application/octet-stream") == 0) {
+        auto id = req.headers.find("x-request-id");
+        if (id == req.headers.end()) throw std::runtime_error("octet-stream request without an X-Request-Id header");
+        if (id->second.find_first_of("\r\n") != std::string::npos) throw std::runtime_error("bad X-Request-Id header");
+        res.set_content(gateway.routeRaw(id->second, req.body), "application/json");
+        return;
+      }
       res.set_content(gateway.route(req.body), "application/json");
     } catch (const std::exception& e) {
       json error;

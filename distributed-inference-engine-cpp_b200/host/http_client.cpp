@@ -124,9 +124,10 @@ int ClientPool::connect_new(std::string& err) const {
 }
 
 ClientResult ClientPool::request(const std::string& method, const std::string& path, const std::string& body,
-                                 const std::string& content_type) {
+                                 const std::string& content_type, const std::string& extra_headers) {
   std::string head = method + " " + path + " HTTP/1.1\r\nHost: " + host_ + ":" + std::to_string(port_) + "\r\nConnection: keep-alive\r\n";
   if (method == "POST") head += "Content-Type: " + content_type + "\r\nContent-Length: " + std::to_string(body.size()) + "\r\n";
+  head += extra_headers;
   head += "\r\n";
   for (int attempt = 0; attempt < 2; ++attempt) {
     ClientResult r;
@@ -150,9 +151,10 @@ ClientResult ClientPool::request(const std::string& method, const std::string& p
   return r;
 }
 
-ClientResult ClientPool::Post(const std::string& path, const std::string& body, const std::string& content_type) {
-  return request("POST", path, body, content_type);
+ClientResult ClientPool::Post(const std::string& path, const std::string& body, const std::string& content_type,
+                              const std::string& extra_headers) {
+  return request("POST", path, body, content_type, extra_headers);
 }
-ClientResult ClientPool::Get(const std::string& path) { return request("GET", path, "", ""); }
+ClientResult ClientPool::Get(const std::string& path) { return request("GET", path, "", "", ""); }
 
 }  // namespace mini_http

@@ -23,11 +23,14 @@ class ClientPool {
   ClientPool(const ClientPool&) = delete;
   ClientPool& operator=(const ClientPool&) = delete;
   // POST `body` to `path`; retries once on a fresh connection if a pooled keep-alive connection turns out dead.
-  ClientResult Post(const std::string& path, const std::string& body, const std::string& content_type);
+  // extra_headers: complete "Name: value\r\n" lines appended to the request head
+  ClientResult Post(const std::string& path, const std::string& body, const std::string& content_type,
+                    const std::string& extra_headers = "");
   ClientResult Get(const std::string& path);
 
  private:
-  ClientResult request(const std::string& method, const std::string& path, const std::string& body, const std::string& content_type);
+  ClientResult request(const std::string& method, const std::string& path, const std::string& body, const std::string& content_type,
+                       const std::string& extra_headers);
   int take();               // an idle connection or -1
   void give(int fd);
   int connect_new(std::string& err) const;

@@ -5,6 +5,7 @@
 // Build with -DWORKER_FAKE_ENGINE for a CPU-only binary whose "engine" returns a checksum row per sample
 // (used by the host-side tests of the JSON contract; never by the product).
 #include <cstdlib>
+#include <cstring>
 #include <iostream>
 
 #include "http_server.h"
@@ -56,6 +57,18 @@ int main(int argc, char** argv) {
     try {
       // B200RN_FAST_JSON=0 forces the reference's parse-then-convert path for every body (A/B and tests)
       static const bool fast = !(std::getenv("B200RN_FAST_JSON") && std::getenv("B200RN_FAST_JSON")[0] == '0');
+      // Additive side channel: Content-Type application/octet-stream carries the sample as raw
+      // little-endian float32 and the id in X-Request-Id; the response is the usual JSON.  JSON stays the default.
+      auto ct = req.headers.find("content-type");
+      if (ct != req.headers.end() && ct->second.compare(0, 24, "application/octet-stream") == 0) {
+        auto id = req.headers.find("x-request-id");
+        if (id == req.headers.end()) throw std::runtime_error("octet-stream request without an X-Request-Id header");
+        if (req.body.size() % sizeof(float)) throw std::runtime_error("octet-stream body is not a whole number of float32 values");
+        std::vector<float> data(req.body.size() / sizeof(float));
+        std::memcpy(data.data(), req.body.data(), req.body.size());
+        res.set_content(worker.handleInferRaw(id->second, data).dump(), "application/json");
+        return;
+      }
       if (fast) res.set_content(worker.handleInferBody(req.body).dump(), "application/json");
       else res.set_content(worker.handleInfer(json::parse(req.body)).dump(), "application/json");
     } catch (const std::exception& e) {

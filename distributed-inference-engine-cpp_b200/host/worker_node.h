@@ -67,6 +67,12 @@ class WorkerNodeT {
     return handleInfer(json::parse(body));
   }
 
+  // Entry for requests whose fields arrive already decoded (the octet-stream side channel).
+  json handleInferRaw(const std::string& request_id, const std::vector<float>& input_data) {
+    ++total_requests_;
+    return handleInferFields(request_id, input_data);
+  }
+
   json handleInfer(const json& request) {
     ++total_requests_;
     // A missing key reads as null and the conversion then throws nlohmann's type_error.302

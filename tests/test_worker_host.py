@@ -176,3 +176,21 @@ def test_fast_scanner_random_numbers(worker_pair):
         b = requests.post(slow + "/infer", data=body, timeout=5).json()
         a.pop("inference_time_us", None), b.pop("inference_time_us", None)
         assert a == b, body
+
+
+def test_octet_stream_side_channel_equals_json(worker_pair):
+    """Additive raw-float32 request form: same response bytes as the JSON form of the same sample (cache hit, so the
+    timing field is the constant 50), its own error texts, JSON untouched."""
+    import numpy as np
+    url = worker_pair[0]
+    x = np.array([0.25, -3.5, 1e-8, 16777217.0, 0.1], dtype=np.float32)
+    j = requests.post(url + "/infer", json={"request_id": "sc", "input_data": [float(v) for v in x]}, timeout=5)
+    assert j.status_code == 200
+    hdr = {"Content-Type": "application/octet-stream", "X-Request-Id": "sc"}
+    r = requests.post(url + "/infer", data=x.tobytes(), headers=hdr, timeout=5)
+    j2 = requests.post(url + "/infer", json={"request_id": "sc", "input_data": [float(v) for v in x]}, timeout=5)
+    assert r.status_code == 200 and r.text == j2.text and '"cached":true' in r.text
+    r = requests.post(url + "/infer", data=x.tobytes()[:-1], headers=hdr, timeout=5)
+    assert r.status_code == 500 and "whole number of float32" in r.json()["error"]
+    r = requests.post(url + "/infer", data=x.tobytes(), headers={"Content-Type": "application/octet-stream"}, timeout=5)
+    assert r.status_code == 500 and "X-Request-Id" in r.json()["error"]

@@ -24,7 +24,7 @@ import b200rn_loader  # noqa: E402
 import bench  # noqa: E402
 
 
-def run(url, payloads, threads):
+def run(url, payloads, threads, raw_ids=None):
     lat, lock = [], threading.Lock()
     per = len(payloads) // threads
 
@@ -33,7 +33,9 @@ def run(url, payloads, threads):
         for k in range(per):
             i = t * per + k
             t0 = time.time()
-            r = s.post(url + "/infer", data=payloads[i], headers={"Content-Type": "application/json"}, timeout=60)
+            hdr = ({"Content-Type": "application/json"} if raw_ids is None else
+                   {"Content-Type": "application/octet-stream", "X-Request-Id": raw_ids[i]})
+            r = s.post(url + "/infer", data=payloads[i], headers=hdr, timeout=60)
             dt = (time.time() - t0) * 1000
             if r.status_code == 200:
                 with lock:
@@ -115,6 +117,14 @@ def main():
             big.append(json.dumps({"request_id": "req_%d" % i, "input_data": x.tolist()}))
         out["payload_bytes"] = len(big[0])
         out["inference_path_150528_floats"] = run(url, big, a.threads)
+        # the additive raw-float32 form of the same requests (octet-stream body, id in X-Request-Id)
+        raws, ids = [], []
+        for i in range(a.requests):
+            x = base.copy()
+            x[0] = float(i) + 0.5                # unique again: no cache hits
+            raws.append(x.tobytes())
+            ids.append("raw_%d" % i)
+        out["inference_path_octet_stream"] = run(url, raws, a.threads, ids)
         out["config"] = {"workers": a_workers, "gpus": ngpu, "gateway": bool(a.gateway), "threads": a.threads, "mode": a.mode}
         out["health"] = [requests.get("http://" + ad + "/health", timeout=5).json() for ad in addrs]
         if a.gateway:
