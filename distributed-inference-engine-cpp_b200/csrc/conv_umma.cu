@@ -37,6 +37,7 @@ constexpr int kEpiWarps = 8;                       // two warps per TMEM lane qu
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kBaseThreads = 64 + kEpiThreads;     // TMA warp, MMA warp, epilogue warps
 constexpr int kThreads = kBaseThreads + 128;       // + 4 operand-transform warps (layers with a prologue only)
+constexpr int kTwoGroupThreads = 64 + 2 * kEpiThreads;   // kernels whose epilogue runs as two 8-warp groups on alternating tiles
 constexpr int kTileM = 128;
 constexpr int kChunkBytes = kTileM * 128;  // one 64-channel output chunk of a tile (16 KB)
 
@@ -627,7 +628,7 @@ struct HaloParams {
 };
 
 template <typename T, int BLOCK_N>
-__global__ void __launch_bounds__(kBaseThreads, 1)
+__global__ void __launch_bounds__(kTwoGroupThreads, 1)
 conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_constant__ CUtensorMap tmW,
                     const __grid_constant__ CUtensorMap tmOutRow, const HaloParams p) {
   constexpr int kChunks = BLOCK_N / 64;
@@ -641,8 +642,8 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_con
   uint8_t* halo = smem;
   uint8_t* bbuf = halo + HS * kHaloStageBytes;                     // stationary slab or ring of SB tiles
   uint8_t* outbuf = bbuf + (p.b_stationary ? kblocks : SB) * B_BYTES;  // 2 x [kChunks x 16 KB]
-  float* s_bias = reinterpret_cast<float*>(outbuf + 2 * OUT_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_bias + BLOCK_N);
+  float* s_bias_all = reinterpret_cast<float*>(outbuf + 2 * OUT_BYTES);     // one copy per epilogue group
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_bias_all + 2 * BLOCK_N);
   uint64_t* halo_full = bars;                 // [HS]
   uint64_t* halo_empty = halo_full + HS;      // [HS]
   uint64_t* b_full = halo_empty + HS;         // [SB] (b_full[0] doubles as "slab landed" when stationary)
@@ -785,28 +786,35 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_con
     }
   } else {
     // ===== epilogue: bias + ReLU; the 14 valid pixels of each row are packed densely, one TMA store per chunk =====
+    // Two groups of 8 warps; group k takes the tiles with (i & 1) == k, i.e. it owns TMEM accumulator k and staging
+    // buffer k.  One tile's epilogue is a ~2300-cycle latency chain (TMEM load, ~150 dependent ALU ops per thread,
+    // smem stores, proxy fence, barrier, store issue) that the MMA thread used to wait ~700 cycles per tile for
+    // (timeline, B200RN_DBG_TRACE); with two chains in flight it no longer does.
+    const int grp = (warp - 2) >> 3;
     const int q4 = warp & 3;
-    const int g = (warp - 2) >> 2;
+    const int g = ((warp - 2) & 7) >> 2;
+    float* s_bias = s_bias_all + grp * BLOCK_N;
     const int row = q4 * 32 + lane;                       // TMEM lane = y*16 + x
     const bool valid = (row & 15) < kHaloBW;              // x = 14, 15 are the junk columns
     const int drow = (row >> 4) * kHaloBW + (row & 15);   // dense staging row y*14 + x
     const int sw = drow & 7;
-    const int et = threadIdx.x - 64;
-    const bool store_thread = (warp == 2 && lane == 0);
+    const int et = threadIdx.x - 64 - grp * kEpiThreads;
+    const bool store_thread = (((warp - 2) & 7) == 0 && lane == 0);
+    const int bar_id = 1 + grp;
     int cur_ntile = -1;
-    for (int i = 0; i < my_tiles; ++i) {
+    for (int i = grp; i < my_tiles; i += 2) {
       const int tile = int(blockIdx.x) + i * int(gridDim.x);
       int x0, y0, n, col0;
       tile_coord(tile, x0, y0, n, col0);
-      const int buf = i & 1;
+      const int buf = grp;
       if (tile % p.n_tiles != cur_ntile) {
         cur_ntile = tile % p.n_tiles;
         for (int k = et; k < BLOCK_N; k += kEpiThreads) s_bias[k] = __ldg(p.bias + col0 + k);
       }
       const bool tr = false;
       if (tr) p.trace[i * 8 + 4] = clock64();
-      if (store_thread && i > 0) tma_store_wait_read_pending<kChunks>();   // tile i-2's staging is free again
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (store_thread && i > grp) tma_store_wait_read();   // this group's previous tile has left its staging buffer
+      asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
       if (tr) p.trace[i * 8 + 5] = clock64();
       mbar_wait(smem_u32(&tmem_full[buf]), (i >> 1) & 1);
       tc_fence_after();
@@ -843,7 +851,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_con
           }
         }
         fence_proxy_async_smem();
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
         if (store_thread && !(p.dbg_skip & 2)) {
           tma_store_4d(&tmOutRow, smem_u32(stage), col0 + c * 64, x0, y0, n);   // box {64 ch, 14, 8, 1}
           tma_store_commit();
@@ -899,7 +907,7 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* m, 
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kBaseThreads, 1)
+__global__ void __launch_bounds__(kTwoGroupThreads, 1)
 stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constant__ CUtensorMap tmOut, const Stem2Params p) {
   constexpr int BLOCK_N = 64;
   extern __shared__ uint8_t smem_raw[];
@@ -931,7 +939,7 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
   }
   if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * BLOCK_N);
   if (warp >= 2)
-    for (int k = threadIdx.x - 64; k < BLOCK_N; k += kEpiThreads) s_bias[k] = __ldg(p.bias + n_tile * BLOCK_N + k);
+    for (int k = threadIdx.x - 64; k < BLOCK_N; k += 2 * kEpiThreads) s_bias[k] = __ldg(p.bias + n_tile * BLOCK_N + k);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -992,17 +1000,21 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
       }
     }
   } else {
+    // two groups of 8 epilogue warps on alternating tiles (group k owns accumulator k and staging buffer k): a tile's
+    // epilogue is a ~2000-cycle latency chain against ~700 cycles of MMAs, so one chain at a time set the pace
+    const int grp = (warp - 2) >> 3;
     const int q4 = warp & 3;
-    const int g = (warp - 2) >> 2;
+    const int g = ((warp - 2) & 7) >> 2;
     const int row = q4 * 32 + lane;            // = y*8 + x, the order the {64, 8, 16, 1} store box expects
     const int sw = row & 7;
-    const bool store_thread = (warp == 2 && lane == 0);
-    for (int i = 0; i < my_tiles; ++i) {
+    const bool store_thread = (((warp - 2) & 7) == 0 && lane == 0);
+    const int bar_id = 1 + grp;
+    for (int i = grp; i < my_tiles; i += 2) {
       int x0, y0, n;
       tile_coord(i, x0, y0, n);
-      const int buf = i & 1;
-      if (store_thread && i > 0) tma_store_wait_read_pending<1>();   // tile i-2's staging buffer is free again
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      const int buf = grp;
+      if (store_thread && i > grp) tma_store_wait_read();   // this group's previous tile has left its staging buffer
+      asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
       mbar_wait(smem_u32(&tmem_full[buf]), (i >> 1) & 1);
       tc_fence_after();
       uint32_t acc[32];
@@ -1029,7 +1041,7 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
         out_row[j ^ sw] = make_uint4(pack2<T>(v[0], v[1]), pack2<T>(v[2], v[3]), pack2<T>(v[4], v[5]), pack2<T>(v[6], v[7]));
       }
       fence_proxy_async_smem();
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
       if (store_thread) {
         tma_store_4d(&tmOut, smem_u32(stage_out), n_tile * BLOCK_N, x0, y0, n);   // box {64 ch, 8, 16, 1}
         tma_store_commit();
@@ -1059,7 +1071,7 @@ struct DualParams {
 };
 
 template <typename T, int BLOCK_N>
-__global__ void __launch_bounds__(kBaseThreads, 1)
+__global__ void __launch_bounds__(kTwoGroupThreads, 1)
 conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                   const __grid_constant__ CUtensorMap tmOut, const DualParams p) {
   constexpr int kChunks = BLOCK_N / 64;
@@ -1071,7 +1083,7 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int S = p.num_stages;
   uint8_t* pipe = smem;
-  uint8_t* outbuf = pipe + S * STAGE_BYTES;        // two 16 KB chunk buffers, used alternately
+  uint8_t* outbuf = pipe + S * STAGE_BYTES;        // two 16 KB chunk buffers, one per epilogue group
   float* s_bias = reinterpret_cast<float*>(outbuf + 2 * kChunkBytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_bias + BLOCK_N);
   uint64_t* full_bar = bars;
@@ -1089,7 +1101,7 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     prefetch_tmap(&tmOut);
     for (int i = 0; i < S; ++i) { mbar_init(smem_u32(&full_bar[i]), 1); mbar_init(smem_u32(&empty_bar[i]), 1); }
     mbar_init(smem_u32(tmem_full), 1);
-    mbar_init(smem_u32(tmem_empty), kEpiThreads);
+    mbar_init(smem_u32(tmem_empty), 2 * kEpiThreads);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * BLOCK_N);
@@ -1162,14 +1174,20 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       }
     }
   } else {
+    // Two groups of 8 epilogue warps: group h drains accumulator h (M tile h of the item) through its own staging
+    // buffer.  Nothing overlaps this epilogue (both accumulators are in use), so halving its length is a direct gain:
+    // 8 chunks in lock step were ~12k cycles beside ~37k of MMAs on the 3x3 @14x14 layers.
+    const int grp = (warp - 2) >> 3;
     const int q4 = warp & 3;
-    const int g = (warp - 2) >> 2;
+    const int g = ((warp - 2) & 7) >> 2;
     const int row = q4 * 32 + lane;
     const int sw = row & 7;
-    const int et = threadIdx.x - 64;
-    const bool store_thread = (warp == 2 && lane == 0);
+    const int et = threadIdx.x - 64;             // 0..511 over both groups
+    const bool store_thread = (((warp - 2) & 7) == 0 && lane == 0);
+    const int bar_id = 1 + grp;
+    uint8_t* stage_out = outbuf + grp * kChunkBytes;
     int cur_ntile = -1;
-    int cc = 0;                                  // running chunk counter: staging buffer = cc & 1
+    int cc = 0;                                  // this group's running chunk counter
     for (int i = 0; i < my_items; ++i) {
       const int item = int(blockIdx.x) + i * int(gridDim.x);
       const int n_tile = item % p.n_tiles;
@@ -1177,13 +1195,15 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       const int pm = item / p.n_tiles;
       if (n_tile != cur_ntile) {
         cur_ntile = n_tile;
-        asm volatile("bar.sync 1, 256;" ::: "memory");      // nobody still reads the previous bias set
-        for (int k = et; k < BLOCK_N; k += kEpiThreads) s_bias[k] = __ldg(p.bias + col0 + k);
+        // both groups walk the same item list, so they meet here: nobody still reads the previous bias set
+        asm volatile("bar.sync 3, 512;" ::: "memory");
+        for (int k = et; k < BLOCK_N; k += 2 * kEpiThreads) s_bias[k] = __ldg(p.bias + col0 + k);
+        asm volatile("bar.sync 3, 512;" ::: "memory");
       }
       mbar_wait(smem_u32(tmem_full), uint32_t(i) & 1);
       tc_fence_after();
-#pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
+      {
+        const int h = grp;
         int w0, h0, n0;
         m_coord(2 * pm + h, w0, h0, n0);
 #pragma unroll 1
@@ -1191,14 +1211,12 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           uint32_t acc[32];
           tmem_ld_32x32b_x32(tmem_base + (uint32_t(q4 * 32) << 16) + uint32_t(h * BLOCK_N + c * 64 + g * 32), acc);
           tmem_ld_wait();
-          if (h == 1 && c == kChunks - 1) {
+          if (c == kChunks - 1) {
             tc_fence_before();
             mbar_arrive(smem_u32(tmem_empty));
           }
-          // the buffer about to be rewritten was stored two chunks ago: let only the latest store pend
-          if (store_thread && cc >= 2) tma_store_wait_read_pending<1>();
-          asm volatile("bar.sync 1, 256;" ::: "memory");
-          uint8_t* stage_out = outbuf + (cc & 1) * kChunkBytes;
+          if (store_thread && cc > 0) tma_store_wait_read();   // the previous chunk's store has read the staging buffer
+          asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
           uint4* out_row = reinterpret_cast<uint4*>(stage_out + row * 128);
 #pragma unroll
           for (int jj = 0; jj < 4; ++jj) {
@@ -1218,7 +1236,7 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             out_row[j ^ sw] = make_uint4(pack2<T>(v[0], v[1]), pack2<T>(v[2], v[3]), pack2<T>(v[4], v[5]), pack2<T>(v[6], v[7]));
           }
           fence_proxy_async_smem();
-          asm volatile("bar.sync 1, 256;" ::: "memory");
+          asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
           if (store_thread) {
             tma_store_4d(&tmOut, smem_u32(stage_out), col0 + c * 64, w0, h0, n0);
             tma_store_commit();
@@ -1556,7 +1574,7 @@ static cudaError_t launch_halo(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  return launch_pdl(kern, pl->grid, kBaseThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmOut, pl->hp);
+  return launch_pdl(kern, pl->grid, kTwoGroupThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmOut, pl->hp);
 }
 
 template <typename T>
@@ -1570,7 +1588,7 @@ static cudaError_t launch_stem2(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  return launch_pdl(kern, pl->grid, kBaseThreads, pl->smem_bytes, s, pl->tmA, pl->tmOut, pl->sp);
+  return launch_pdl(kern, pl->grid, kTwoGroupThreads, pl->smem_bytes, s, pl->tmA, pl->tmOut, pl->sp);
 }
 
 template <typename T, int BLOCK_N>
@@ -1584,7 +1602,7 @@ static cudaError_t launch_dual(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  return launch_pdl(kern, pl->grid, kBaseThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmOut, pl->dp);
+  return launch_pdl(kern, pl->grid, kTwoGroupThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmOut, pl->dp);
 }
 
 template <typename T, int N1>
@@ -1797,7 +1815,7 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       hp.b_stationary = (slab <= 80u * 1024 && hp.total_tiles >= 2 * grid) ? 1 : 0;
       hp.b_stages = hp.b_stationary ? 1 : 4;
       const uint32_t fixed = 1024u + (hp.b_stationary ? slab : uint32_t(hp.b_stages) * b_bytes) + 2 * out_bytes +
-                             uint32_t(pl->block_n) * 4 + 8u * (2 * 8 + 2 * 4 + 4) + 64;
+                             2u * uint32_t(pl->block_n) * 4 + 8u * (2 * 8 + 2 * 4 + 4) + 64;
       hp.halo_stages = std::max(2, std::min(8, int((budget - fixed) / kHaloStageBytes)));
       pl->smem_bytes = fixed + uint32_t(hp.halo_stages) * kHaloStageBytes;
       pl->grid = grid;
