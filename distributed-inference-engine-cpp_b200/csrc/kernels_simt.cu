@@ -559,10 +559,91 @@ size_t simt_splitk_scratch_bytes(int max_rows, int Cout) {
   return (tiles * 4 + 255) / 256 * 256 + size_t(16) * max_rows * Cout * 4;
 }
 
+// 3x3 / stride 2 / pad 1 max-pool on 16-bit NHWC (the ResNet stem's pool), two horizontally adjacent outputs per
+// thread: 15 window loads for two outputs instead of 18, and the max stays in the packed 16-bit type (max is exact,
+// so no conversion to fp32 and back is needed; NaNs are ignored like fmaxf does).  Padding taps are skipped.
+template <typename T> struct Pk;
+template <> struct Pk<__half> {
+  using V2 = __half2;
+  __device__ static V2 lowest() { return __half2half2(__ushort_as_half(0xFBFFu)); }       // -65504
+  __device__ static float2 to_float2(V2 v) { return __half22float2(v); }
+};
+template <> struct Pk<__nv_bfloat16> {
+  using V2 = __nv_bfloat162;
+  __device__ static V2 lowest() { return __bfloat162bfloat162(__ushort_as_bfloat16(0xFF7Fu)); }   // -3.39e38
+  __device__ static float2 to_float2(V2 v) { return __bfloat1622float2(v); }
+};
+
+template <typename T>
+__global__ void maxpool3x3s2_pair_kernel(const T* __restrict__ in, int B, int H, int W, int C, int Ho, int Wo, Epilogue e) {
+  using V2 = typename Pk<T>::V2;
+  const int cv = C / 8;
+  const int Wp = (Wo + 1) / 2;                                  // output pairs per row
+  int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int64_t total = int64_t(B) * Ho * Wp * cv;
+  if (idx >= total) return;
+  const int c = int(idx % cv) * 8;
+  int64_t t = idx / cv;
+  const int wp = int(t % Wp); t /= Wp;
+  const int ho = int(t % Ho);
+  const int b = int(t / Ho);
+  const int wo = 2 * wp;
+  V2 best[2][4];
+#pragma unroll
+  for (int o = 0; o < 2; ++o)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) best[o][i] = Pk<T>::lowest();
+  const int iw0 = wo * 2 - 1;                                   // columns iw0 .. iw0+4 cover both windows
+#pragma unroll
+  for (int ky = 0; ky < 3; ++ky) {
+    const int ih = ho * 2 - 1 + ky;
+    if (ih < 0 || ih >= H) continue;
+    const T* rowp = in + (int64_t(b) * H + ih) * W * C + c;
+#pragma unroll
+    for (int kx = 0; kx < 5; ++kx) {
+      const int iw = iw0 + kx;
+      if (iw < 0 || iw >= W) continue;
+      const uint4 x = __ldg(reinterpret_cast<const uint4*>(rowp + int64_t(iw) * C));
+      const V2* h = reinterpret_cast<const V2*>(&x);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (kx <= 2) best[0][i] = __hmax2(best[0][i], h[i]);
+        if (kx >= 2) best[1][i] = __hmax2(best[1][i], h[i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 0; o < 2; ++o) {
+    if (wo + o >= Wo) break;
+    const int64_t off = ((int64_t(b) * Ho + ho) * Wo + wo + o) * C + c;
+    if (e.out) *reinterpret_cast<uint4*>(static_cast<T*>(e.out) + off) = *reinterpret_cast<const uint4*>(best[o]);
+    if (e.out_act) {
+      float a[8];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 f = Pk<T>::to_float2(best[o][i]);
+        a[2 * i] = fmaf(__ldg(e.act_scale + c + 2 * i), f.x, __ldg(e.act_shift + c + 2 * i));
+        a[2 * i + 1] = fmaf(__ldg(e.act_scale + c + 2 * i + 1), f.y, __ldg(e.act_shift + c + 2 * i + 1));
+        if (e.act_relu) { a[2 * i] = fmaxf(a[2 * i], 0.f); a[2 * i + 1] = fmaxf(a[2 * i + 1], 0.f); }
+      }
+      Vec<T>::store(static_cast<T*>(e.out_act) + off, a);
+    }
+  }
+}
+
 cudaError_t launch_maxpool(const void* in, DType dt, int B, int H, int W, int C, int Ho, int Wo, int k, int stride,
                            int pad, const Epilogue& e, cudaStream_t s) {
   int V = dt == DType::F32 ? 4 : 8;
   if (C % V) return cudaErrorInvalidValue;
+  if (dt != DType::F32 && k == 3 && stride == 2 && pad == 1 && H >= 2 && W >= 2) {
+    const int64_t pairs = int64_t(B) * Ho * ((Wo + 1) / 2) * (C / 8);
+    const int pblock = 256, pgrid = grid_for(pairs, pblock);
+    if (dt == DType::BF16)
+      maxpool3x3s2_pair_kernel<__nv_bfloat16><<<pgrid, pblock, 0, s>>>(static_cast<const __nv_bfloat16*>(in), B, H, W, C, Ho, Wo, e);
+    else
+      maxpool3x3s2_pair_kernel<__half><<<pgrid, pblock, 0, s>>>(static_cast<const __half*>(in), B, H, W, C, Ho, Wo, e);
+    return cudaGetLastError();
+  }
   int64_t total = int64_t(B) * Ho * Wo * (C / V);
   int block = 256, grid = grid_for(total, block);
   switch (dt) {
