@@ -58,6 +58,8 @@ struct UmmaParams {
   const float* act_shift;
   const float* pre_scale;
   const float* pre_shift;
+  float* out_f32;           // fp32 row output instead of 16-bit tiles (1x1 spatial outputs: row = image)
+  int f32_ld, f32_cols, f32_rows;
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------------
@@ -569,6 +571,20 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const float2 r0 = unpack2<T>(r.x), r1 = unpack2<T>(r.y), r2 = unpack2<T>(r.z), r3 = unpack2<T>(r.w);
             v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
             v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
+          }
+          if (p.out_f32) {
+            const int img = tc.n0 + row, cg = tc.col0 + col;
+            if (row < int(p.rows) && img < p.f32_rows) {
+              float* dst = p.out_f32 + size_t(img) * p.f32_ld + cg;
+              if (cg + 8 <= p.f32_cols && (p.f32_ld & 3) == 0) {
+                *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+                *reinterpret_cast<float4*>(dst + 4) = make_float4(v[4], v[5], v[6], v[7]);
+              } else {
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                  if (cg + k < p.f32_cols) dst[k] = v[k];
+              }
+            }
           }
           if (f_out)
             raw_row[slot] = make_uint4(pack2<T>(v[0], v[1]), pack2<T>(v[2], v[3]), pack2<T>(v[4], v[5]), pack2<T>(v[6], v[7]));
@@ -1682,7 +1698,12 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   if (const char* v = std::getenv("B200RN_DBG_ASHIFT")) p.dbg_ashift = std::atoi(v);
   p.pre_scale = e.pre_scale; p.pre_shift = e.pre_shift;
   if (p.has_pre && (stem_mode || g.kh != 1 || g.kw != 1 || g.pad != 0)) { delete pl; return failmsg("operand prologue needs a 1x1, pad-0 conv"); }
-  if (!p.has_out && !p.has_act) { delete pl; return failmsg("conv with no output"); }
+  p.out_f32 = e.out_f32; p.f32_ld = e.out_f32_ld; p.f32_cols = e.out_f32_cols; p.f32_rows = g.B;
+  if (p.out_f32 && (stem_mode || g.Ho != 1 || g.Wo != 1 || p.has_out || p.has_act || p.has_res || p.has_pre || e.tail_out)) {
+    delete pl;
+    return failmsg("fp32 row output needs a 1x1-spatial conv with no other output, residual, prologue or tail");
+  }
+  if (!p.has_out && !p.has_act && !p.out_f32) { delete pl; return failmsg("conv with no output"); }
   if (e.tail_out) {
     // 1x1 conv (Cout 256) + residual -> raw output, and the following 1x1 conv on relu(bn(.)) of it
     if (stem_mode || g.kh != 1 || g.kw != 1 || g.stride != 1 || g.pad != 0 || g.Cout != kTailN3 || !p.has_res || !p.has_out ||
@@ -2000,7 +2021,7 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     }
   }
   // unused maps still need to be valid objects to pass by value: alias the output map
-  const void* any_out = e.out ? e.out : e.out_act;
+  const void* any_out = e.out ? e.out : (e.out_act ? e.out_act : in);   // fp32-row convs have no 16-bit output: any valid address
   if (ok) ok = encode_act(&pl->tmOut, dt, e.out ? e.out : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
   if (ok) ok = encode_act(&pl->tmAct, dt, e.out_act ? e.out_act : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
   if (ok) ok = encode_act(&pl->tmRes, dt, e.residual ? e.residual : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
@@ -2011,6 +2032,10 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
                  pl->dual ? pl->dp.total_items : p.total_tiles, pl->grid, pl->dual ? pl->dp.num_stages : p.num_stages, p.kgroup,
                  p.b_stationary, pl->smem_bytes);
   return pl;
+}
+
+void umma_conv_plan_set_out_f32(UmmaConvPlan* p, float* out_f32) {
+  if (p && p->p.out_f32) p->p.out_f32 = out_f32;
 }
 
 void umma_conv_plan_destroy(UmmaConvPlan* p) {

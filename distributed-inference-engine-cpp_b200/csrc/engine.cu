@@ -52,6 +52,12 @@ bool tail_enabled() {
   return !(v && v[0] == '0');
 }
 
+// FC on the tensor cores in the 16-bit modes (B200RN_FC_UMMA=0: the fp32 CUDA-core kernel, as in exact mode).
+bool fc_umma_enabled() {
+  const char* v = std::getenv("B200RN_FC_UMMA");
+  return !(v && v[0] == '0');
+}
+
 struct CudaFail { std::string msg; };
 #define CK(expr)                                                                                       \
   do {                                                                                                 \
@@ -71,6 +77,9 @@ struct DevLayer {
   float* pre_scale = nullptr;
   float* pre_shift = nullptr;
   void* w = nullptr;
+  void* fc_in16 = nullptr;              // Gemm on the tensor-core path: its operand rows in the activation type (written by the pool)
+  void* gap_out16 = nullptr;            // Gap: where to put that copy (owned by the Gemm layer)
+  int fc_cout_pad = 0;
   void* tail_w = nullptr;               // fused tail conv: packed weights + bias
   float* tail_bias = nullptr;
   bool umma = false;
@@ -122,7 +131,7 @@ struct b200rn {
     cudaSetDevice(device);
     for (auto& L : dl) {
       cudaFree(L.bias); cudaFree(L.act_scale); cudaFree(L.act_shift); cudaFree(L.w); cudaFree(L.splitk);
-      cudaFree(L.pre_scale); cudaFree(L.pre_shift); cudaFree(L.tail_w); cudaFree(L.tail_bias);
+      cudaFree(L.pre_scale); cudaFree(L.pre_shift); cudaFree(L.tail_w); cudaFree(L.tail_bias); cudaFree(L.fc_in16);
       for (auto& kv : L.plans) umma_conv_plan_destroy(kv.second);
     }
     for (auto& kv : graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
@@ -239,6 +248,30 @@ struct b200rn {
             D.weight_bytes += double(tbytes);
           }
           if (D.stem) stem_tensor = L.in;
+        } else if (L.kind == LayerKind::Gemm && dt != DType::F32 && fc_umma_enabled() && L.Cin % 64 == 0 &&
+                   plan.tensors[size_t(L.in)].def_layer >= 0 &&
+                   plan.layers[size_t(plan.tensors[size_t(L.in)].def_layer)].kind == LayerKind::Gap) {
+          // FC behind a global pool, 16-bit modes: a 1x1 conv over [B,1,1,K] rows on the tensor cores with fp32 rows
+          // out.  The pool writes a second copy of its means in the activation type; the output channels are padded
+          // to a multiple of 64 with zero weights (the epilogue only stores the true ones).
+          const int Npad = (L.Cout + 63) / 64 * 64;
+          ConvGeom g{1, 1, 1, L.Cin, 1, 1, Npad, 1, 1, 1, 0};
+          std::vector<float> wpad(size_t(Npad) * L.Cin, 0.f);
+          std::copy(L.weight.begin(), L.weight.end(), wpad.begin());
+          size_t bytes = umma_weight_bytes(g, 0);
+          std::vector<uint8_t> packed(bytes);
+          umma_pack_weights(wpad.data(), g, dt, 0, packed.data());
+          CK(cudaMalloc(&D.w, bytes));
+          CK(cudaMemcpy(D.w, packed.data(), bytes, cudaMemcpyHostToDevice));
+          D.weight_bytes = double(bytes);
+          std::vector<float> bpad(size_t(Npad), 0.f);
+          std::copy(L.bias.begin(), L.bias.end(), bpad.begin());
+          cudaFree(D.bias);
+          D.bias = upload(bpad);
+          D.umma = true;
+          D.fc_cout_pad = Npad;
+          CK(cudaMalloc(&D.fc_in16, size_t(max_batch) * L.Cin * 2));
+          dl[size_t(plan.tensors[size_t(L.in)].def_layer)].gap_out16 = D.fc_in16;
         } else {
           // fp32 CUDA-core path wants W^T: [K][Cout]
           const int K = L.kind == LayerKind::Gemm ? L.Cin : L.kh * L.kw * L.Cin;
@@ -323,6 +356,22 @@ struct b200rn {
         break;
       }
       case LayerKind::Gemm: {
+        if (D.umma) {
+          ConvGeom g{B, 1, 1, L.Cin, 1, 1, D.fc_cout_pad, 1, 1, 1, 0};
+          UmmaConvPlan*& up = D.plans[B];
+          if (!up) {
+            Epilogue fe;
+            fe.bias = D.bias;
+            fe.out_f32 = static_cast<float*>(out_ptr(L.out));
+            fe.out_f32_ld = L.Cout; fe.out_f32_cols = L.Cout;
+            char msg[512] = {0};
+            up = umma_conv_plan_create(dt, g, D.fc_in16, D.w, fe, 0, msg, sizeof msg);
+            if (!up) { D.plans.erase(B); throw CudaFail{fmt("layer '%s': %s", L.name.c_str(), msg)}; }
+          }
+          umma_conv_plan_set_out_f32(up, static_cast<float*>(out_ptr(L.out)));   // the graph output moves with the caller
+          CK(launch_conv_umma(up, s));
+          break;
+        }
         // [B, K] x W^T[K][N] + bias on the fp32 CUDA-core kernel (a 1x1 conv over a 1x1 image)
         ConvGeom g{B, 1, 1, L.Cin, 1, 1, L.Cout, 1, 1, 1, 0};
         Epilogue ge;
@@ -351,7 +400,7 @@ struct b200rn {
       case LayerKind::Gap: {
         const PlanTensor& in = plan.tensors[size_t(L.in)];
         CK(launch_gap(tptr(L.in), dt, B, in.H * in.W, in.Cpad, in.C, D.act_scale, D.act_shift, L.act_relu,
-                      static_cast<float*>(out_ptr(L.out)), s));
+                      static_cast<float*>(out_ptr(L.out)), s, in.Cpad == in.C ? D.gap_out16 : nullptr));
         break;
       }
       case LayerKind::Softmax: {

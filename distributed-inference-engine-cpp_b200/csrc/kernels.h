@@ -38,6 +38,10 @@ struct Epilogue {
   void* tail_out = nullptr;
   int tail_cout = 0;
   int tail_relu = 0;
+  // fp32 row output (tensor-core path, 1x1 spatial outputs only: the FC as a 1x1 conv over pooled rows):
+  //   out_f32[image][c] = acc + bias[c] for c < out_f32_cols, row pitch out_f32_ld floats; no 16-bit output then.
+  float* out_f32 = nullptr;
+  int out_f32_ld = 0, out_f32_cols = 0;
 };
 
 struct ConvGeom {
@@ -66,8 +70,9 @@ cudaError_t launch_maxpool(const void* in, DType dt, int B, int H, int W, int C,
                            int pad, const Epilogue& e, cudaStream_t s);
 
 // out[b][c] = mean over H*W of relu?(scale[c]*x + shift[c]);  fp32 rows [B, Ctrue]; C = stored channels
+// out16 (optional, 16-bit types only): the same means as [B, C] rows in the activation type (the FC's operand)
 cudaError_t launch_gap(const void* in, DType dt, int B, int HW, int C, int Ctrue, const float* scale,
-                       const float* shift, int relu, float* out, cudaStream_t s);
+                       const float* shift, int relu, float* out, cudaStream_t s, void* out16 = nullptr);
 
 // stand-alone element-wise fallbacks (only used when the graph does not match a fusion)
 cudaError_t launch_affine(const void* in, void* out, DType dt, int64_t pixels, int C, const float* scale,
@@ -81,6 +86,8 @@ struct UmmaConvPlan;  // opaque: TMA descriptors + tile geometry for one conv la
 UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in, const void* w_packed,
                                     const Epilogue& e, int stem_mode, char* err, size_t errcap);
 void umma_conv_plan_destroy(UmmaConvPlan*);
+// fp32-row plans only: the rows' destination may change between launches (it is the caller's output buffer)
+void umma_conv_plan_set_out_f32(UmmaConvPlan*, float* out_f32);
 cudaError_t launch_conv_umma(const UmmaConvPlan* p, cudaStream_t s);
 // bytes of the packed weight buffer and the host-side packer ([Cout][kh][kw][Cin] fp32 -> kernel layout)
 size_t umma_weight_bytes(const ConvGeom& g, int stem_mode);
