@@ -220,9 +220,15 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the B200 backend has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dist = None
+    saved_stdout = None
     if world > 1:
         import torch.distributed as dist
-        os.environ["NCCL_DEBUG"] = "WARN"        # keep NCCL's version banner off stdout: rank 0 prints ONE line
+        # rank 0 prints ONE line on stdout.  NCCL writes its version banner there on the first collective (at
+        # NCCL_DEBUG=WARN too), so until the JSON line is ready stdout is pointed at stderr.
+        os.environ.setdefault("NCCL_DEBUG", "WARN")
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -373,6 +379,10 @@ def main():
             "gpu_launches": launches * K, "launches_per_step": launches,
             "tflops_whole_step": value / world * FLOP_PER_IMAGE / 1e12,
             "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "batch32": b32}
+    if saved_stdout is not None:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
     print(json.dumps(line), flush=True)
     return 0
 
