@@ -306,8 +306,12 @@ struct Builder {
     int ta = tensor_of(n.inputs[0], n), tb = tensor_of(n.inputs[1], n);
     const PlanTensor A = plan.tensors[size_t(ta)], B = plan.tensors[size_t(tb)];
     if (A.C != B.C || A.H != B.H || A.W != B.W || A.vec_f32 != B.vec_f32) fail("Add '" + n.name + "': shapes differ (broadcast is not supported)");
-    // fuse into the Conv that produced one operand, if this Add is that operand's only reader
+    // fuse into the Conv that produced one operand, if this Add is that operand's only reader.  When both sides
+    // qualify (first block of a stage: main-branch 1x1 conv vs projection shortcut) the one with fewer MACs carries
+    // the residual epilogue -- that epilogue is the expensive part of such a layer, and the smaller reduction keeps
+    // its weights resident in shared memory (conv_wide_kernel); on a tie the later one in graph order.
     int best = -1, best_pos = -1, other = -1;
+    double best_macs = 0;
     for (int side = 0; side < 2; ++side) {
       int t = side ? tb : ta;
       const std::string& vname = n.inputs[size_t(side)];
@@ -317,7 +321,8 @@ struct Builder {
       if (P.kind != LayerKind::Conv || P.out != t || P.in2 >= 0 || P.out_act >= 0) continue;
       if (graph_outputs.count(vname) || consumers[vname].size() != 1) continue;
       int pos = int(std::find(order.begin(), order.end(), pit->second) - order.begin());
-      if (pos > best_pos) { best = pit->second; best_pos = pos; other = side ? ta : tb; }
+      const bool better = best < 0 || P.macs_per_sample < best_macs || (P.macs_per_sample == best_macs && pos > best_pos);
+      if (better) { best = pit->second; best_pos = pos; best_macs = P.macs_per_sample; other = side ? ta : tb; }
     }
     if (best >= 0 && ta != tb) {
       PlanLayer& P = layers[size_t(best)];

@@ -6,7 +6,8 @@
 // Fusions are decided from the graph (consumer counts), never from layer names:
 //   Conv -> BN            (BN the only consumer)      : folded into weights + bias
 //   ... -> ReLU           (only consumer)             : epilogue ReLU
-//   ... -> Add(x, other)  (only consumer)             : epilogue residual add
+//   ... -> Add(x, other)  (only consumer)             : epilogue residual add; when both operands come from such
+//                                                       convs (projection block) the one with fewer MACs takes it
 //   T -> BN -> ReLU -> 1x1 convs only              : applied to those convs' A operand while it is
 //                                                       staged in shared memory; no activated copy exists
 //   T -> BN -> ReLU       (T made by Conv/MaxPool)    : otherwise a second epilogue output relu(s*T+t);
