@@ -35,7 +35,10 @@ struct TailParams {
   int cblks, bw, bh, bn, tiles_w, tiles_h, total_tiles;
   int a_stages, r_slots, act_bufs;
   int relu, act_relu, tail_relu;
+  int has_res;                 // 0: no residual tensor (two-input conv: the shortcut is part of the GEMM); the ring is then staging only
+  int k1_blocks, stride_b;     // two-input conv: K blocks [0, k1_blocks) of a tile come from tmA, the rest from tmA2 at stride_b
   int pf_dist;                 // residual L2 prefetch distance in tiles (0 = off)
+  int pf_in_b;                 // second-input L2 prefetch distance in tiles (0 = off)
   uint32_t rows;
   const float* bias;
   const float* act_scale;
@@ -55,8 +58,8 @@ __device__ __forceinline__ TailTile tail_decode(const TailParams& p, int tile) {
 
 template <typename T, int N1>
 __global__ void __launch_bounds__(kTailThreads, 1)
-conv_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-                 const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmRes,
+conv_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
+                 const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmRes,
                  const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmOut1, const TailParams p) {
   constexpr int kChunks = kTailN3 / 64;                 // 64-channel chunks of the wide tensor = K blocks of the tail GEMM
   constexpr int kChunks1 = N1 / 64;
@@ -98,7 +101,7 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tmA); prefetch_tmap(&tmW); prefetch_tmap(&tmW1);
+    prefetch_tmap(&tmA); prefetch_tmap(&tmA2); prefetch_tmap(&tmW); prefetch_tmap(&tmW1);
     prefetch_tmap(&tmRes); prefetch_tmap(&tmOut); prefetch_tmap(&tmOut1);
     mbar_init(smem_u32(w_bar), 1);
     for (int i = 0; i < SA; ++i) { mbar_init(smem_u32(&a_full[i]), 1); mbar_init(smem_u32(&a_empty[i]), 1); }
@@ -109,6 +112,11 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int i = 0; i < kChunks; ++i) mbar_init(smem_u32(&acc3_full[i]), 1);
     mbar_init(smem_u32(&acc1_full[0]), 1); mbar_init(smem_u32(&acc1_full[1]), 1);
     mbar_init(smem_u32(out1_staged), kTailGroupWarps);
+    // no residual tensor: the ring is only the raw output's staging, nothing has to land in a slot.  Its "ready"
+    // barrier is then completed by the store warp itself when a store has read the slot (and once here, for the
+    // first use), so the operand producer is not held back by the ring at all.
+    if (!p.has_res)
+      for (int i = 0; i < SR; ++i) mbar_arrive(smem_u32(&r_full[i]));
     mbar_init(smem_u32(&acc1_empty[0]), kTailGroupWarps); mbar_init(smem_u32(&acc1_empty[1]), kTailGroupWarps);
     mbar_init(smem_u32(out1_free), 1);
     fence_barrier_init();
@@ -139,21 +147,35 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0, cc = 0;
       // experiment knob (B200RN_TAIL_PF, default off): L2 prefetch of a later tile's residual; measured slower
       auto prefetch_tile = [&](int t) {
-        if (t >= p.total_tiles || p.pf_dist == 0) return;
+        if (t >= p.total_tiles || p.pf_dist == 0 || !p.has_res) return;
         const TailTile pt = tail_decode(p, t);
         for (int c = 0; c < kChunks; ++c) tma_prefetch_4d(&tmRes, c * 64, pt.w0, pt.h0, pt.n0);
       };
       for (int j = 0; j < p.pf_dist; ++j) prefetch_tile(int(blockIdx.x) + j * int(gridDim.x));
+      // Two-input conv: the second input was written several layers ago and comes from HBM, and with one A stage its
+      // load cannot be issued until the previous tile's conv3 MMAs are issued -- the MMA thread then sat ~5000 cycles
+      // per tile on that load (timeline).  Its 16 KB per tile are pulled into L2 two tiles ahead.
+      auto prefetch_in_b = [&](int t) {
+        if (p.k1_blocks >= p.cblks || t >= p.total_tiles || p.pf_in_b == 0) return;
+        const TailTile pt = tail_decode(p, t);
+        for (int kb = p.k1_blocks; kb < p.cblks; ++kb)
+          tma_prefetch_4d(&tmA2, (kb - p.k1_blocks) * 64, pt.w0 * p.stride_b, pt.h0 * p.stride_b, pt.n0);
+      };
+      for (int j = 0; j < p.pf_in_b; ++j) prefetch_in_b(int(blockIdx.x) + j * int(gridDim.x));
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
         const TailTile tc = tail_decode(p, tile);
         prefetch_tile(tile + p.pf_dist * int(gridDim.x));
+        prefetch_in_b(tile + p.pf_in_b * int(gridDim.x));
         mbar_wait(smem_u32(&a_empty[stage]), phase ^ 1);
         const uint32_t fb = smem_u32(&a_full[stage]);
         mbar_expect_tx(fb, uint32_t(p.cblks) * p.rows * 128u);
-        for (int kb = 0; kb < p.cblks; ++kb)
-          tma_load_4d(smem_u32(a_ring + (stage * p.cblks + kb) * A_BLOCK), &tmA, fb, kb * 64, tc.w0, tc.h0, tc.n0);
+        for (int kb = 0; kb < p.cblks; ++kb) {
+          const uint32_t dst = smem_u32(a_ring + (stage * p.cblks + kb) * A_BLOCK);
+          if (kb < p.k1_blocks) tma_load_4d(dst, &tmA, fb, kb * 64, tc.w0, tc.h0, tc.n0);
+          else tma_load_4d(dst, &tmA2, fb, (kb - p.k1_blocks) * 64, tc.w0 * p.stride_b, tc.h0 * p.stride_b, tc.n0);
+        }
         if (++stage == SA) { stage = 0; phase ^= 1; }
-        for (int c = 0; c < kChunks; ++c, ++cc) {
+        for (int c = 0; p.has_res && c < kChunks; ++c, ++cc) {
           const uint32_t slot = cc % uint32_t(SR);
           mbar_wait(smem_u32(&r_empty[slot]), ((cc / uint32_t(SR)) & 1) ^ 1);
           const uint32_t bar = smem_u32(&r_full[slot]);
@@ -246,7 +268,7 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           tma_store_4d(&tmOut, smem_u32(r_ring + slot * kChunkBytes), c * 64, tc.w0, tc.h0, tc.n0);
           tma_store_commit();
           tma_store_wait_read();
-          mbar_arrive(smem_u32(&r_empty[slot]));
+          mbar_arrive(smem_u32(p.has_res ? &r_empty[slot] : &r_full[slot]));
           if (c == 1 && i > 0) store_out1(prev, i - 1);
         }
         prev = tc;
@@ -337,8 +359,10 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint32_t act_row = smem_u32(actb + ab * kChunkBytes) + row_off;
         const uint32_t pcol = uint32_t(c * 64 + g * 32) * 4;       // byte offset of this thread's first channel in the parameter rows
         uint4 res[4];
+        if (p.has_res) {
 #pragma unroll
-        for (int jj = 0; jj < 4; ++jj) res[jj] = lds_u4(raw_row + uint32_t(((g * 4 + jj) ^ sw) << 4));
+          for (int jj = 0; jj < 4; ++jj) res[jj] = lds_u4(raw_row + uint32_t(((g * 4 + jj) ^ sw) << 4));
+        }
         tmem_ld_wait();
         if (tr) trace[cc * 8 + 4] = clock64();
 #pragma unroll
@@ -354,9 +378,11 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
             for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
           }
-          const float2 r0 = unpack2<T>(res[jj].x), r1 = unpack2<T>(res[jj].y), r2 = unpack2<T>(res[jj].z), r3 = unpack2<T>(res[jj].w);
-          v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
-          v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
+          if (p.has_res) {
+            const float2 r0 = unpack2<T>(res[jj].x), r1 = unpack2<T>(res[jj].y), r2 = unpack2<T>(res[jj].z), r3 = unpack2<T>(res[jj].w);
+            v[0] += r0.x; v[1] += r0.y; v[2] += r1.x; v[3] += r1.y;
+            v[4] += r2.x; v[5] += r2.y; v[6] += r3.x; v[7] += r3.y;
+          }
           sts_u4(raw_row + slot16, make_uint4(pack2<T>(v[0], v[1]), pack2<T>(v[2], v[3]), pack2<T>(v[4], v[5]), pack2<T>(v[6], v[7])));
           const float4 s0 = lds_f4(s_scale_a + pcol + jj * 32), s1 = lds_f4(s_scale_a + pcol + jj * 32 + 16);
           const float4 t0 = lds_f4(s_shift_a + pcol + jj * 32), t1 = lds_f4(s_shift_a + pcol + jj * 32 + 16);

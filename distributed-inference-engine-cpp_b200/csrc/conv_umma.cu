@@ -1349,6 +1349,7 @@ struct UmmaConvPlan {
   int tail = 0;           // 1x1 conv + residual fused with the following 1x1 conv (conv_tail_kernel)
   TailParams tp;
   CUtensorMap tmW1, tmOut1;
+  CUtensorMap tmA2;       // second input of a two-input conv (wide / tail kernels)
   int tp_n1 = 0;
 };
 
@@ -1632,7 +1633,7 @@ static cudaError_t launch_tail(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  return launch_pdl(kern, pl->grid, kTailThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmW1, pl->tmRes, pl->tmOut, pl->tmOut1, pl->tp);
+  return launch_pdl(kern, pl->grid, kTailThreads, pl->smem_bytes, s, pl->tmA, pl->tmA2, pl->tmW, pl->tmW1, pl->tmRes, pl->tmOut, pl->tmOut1, pl->tp);
 }
 
 template <typename T, int N>
@@ -1646,7 +1647,7 @@ static cudaError_t launch_wide(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  return launch_pdl(kern, pl->grid, kWideThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->wp);
+  return launch_pdl(kern, pl->grid, kWideThreads, pl->smem_bytes, s, pl->tmA, pl->tmA2, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->wp);
 }
 
 cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
@@ -1706,18 +1707,20 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   if (!p.has_out && !p.has_act && !p.out_f32) { delete pl; return failmsg("conv with no output"); }
   if (e.tail_out) {
     // 1x1 conv (Cout 256) + residual -> raw output, and the following 1x1 conv on relu(bn(.)) of it
-    if (stem_mode || g.kh != 1 || g.kw != 1 || g.stride != 1 || g.pad != 0 || g.Cout != kTailN3 || !p.has_res || !p.has_out ||
+    if (stem_mode || g.kh != 1 || g.kw != 1 || g.stride != 1 || g.pad != 0 || g.Cout != kTailN3 || (!p.has_res && !e.in_b) || !p.has_out ||
         p.has_act || p.has_pre || !e.act_scale || !e.act_shift || !e.tail_w || !e.tail_bias ||
         (e.tail_cout != 64 && e.tail_cout != 128)) {
       delete pl;
-      return failmsg("fused tail conv needs a 1x1/s1/p0 conv to 256 channels with a residual and a raw output, and a 64- or 128-channel tail");
+      return failmsg("fused tail conv needs a 1x1/s1/p0 conv to 256 channels with a residual or a second input and a raw output, and a 64- or 128-channel tail");
     }
     TailParams& tp = pl->tp;
     std::memset(&tp, 0, sizeof tp);
     pl->tail = 1; pl->tp_n1 = e.tail_cout; pl->kb = 128; pl->block_n = kTailN3;
     int bw = 1, bh = 1, bn = 1;
     choose_patch(g.B, g.Ho, g.Wo, bw, bh, bn);
-    tp.cblks = g.Cin / 64;
+    const int tKtot = g.Cin + (e.in_b ? e.in_b_cin : 0);
+    tp.cblks = tKtot / 64; tp.k1_blocks = g.Cin / 64; tp.stride_b = e.in_b ? e.in_b_stride : 1;
+    tp.has_res = p.has_res;
     tp.bw = bw; tp.bh = bh; tp.bn = bn;
     tp.tiles_w = (g.Wo + bw - 1) / bw; tp.tiles_h = (g.Ho + bh - 1) / bh;
     tp.total_tiles = tp.tiles_w * tp.tiles_h * ((g.B + bn - 1) / bn);
@@ -1726,6 +1729,8 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     {
       const char* penv = std::getenv("B200RN_TAIL_PF");
       tp.pf_dist = penv ? std::max(0, std::min(4, std::atoi(penv))) : 0;   // measured: 2 makes the layer 5 % slower
+      const char* p2env = std::getenv("B200RN_TAIL_PF_INB");
+      tp.pf_in_b = p2env ? std::max(0, std::min(4, std::atoi(p2env))) : 2;
     }
     tp.bias = e.bias; tp.act_scale = e.act_scale; tp.act_shift = e.act_shift; tp.tail_bias = e.tail_bias;
     if (std::getenv("B200RN_DBG_TRACE")) {
@@ -1743,9 +1748,18 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     pl->grid = std::min(tp.total_tiles, sm_count());
     std::string tmsg;
     bool tok = encode_act(&pl->tmA, dt, in, g.B, g.H, g.W, g.Cin, bw, bh, bn, 1, tmsg);
+    if (tok && e.in_b) {
+      if (e.in_b_cin % 64 || (e.in_b_h - 1) / e.in_b_stride + 1 != g.Ho || (e.in_b_w - 1) / e.in_b_stride + 1 != g.Wo) {
+        delete pl;
+        return failmsg("two-input conv: the second input must have 64-multiple channels and map onto the output grid at its stride");
+      }
+      tok = encode_act(&pl->tmA2, dt, e.in_b, g.B, e.in_b_h, e.in_b_w, e.in_b_cin, bw, bh, bn, e.in_b_stride, tmsg);
+    } else {
+      pl->tmA2 = pl->tmA;
+    }
     if (tok) {
-      uint64_t wd[2] = {uint64_t(g.Cin), uint64_t(kTailN3)};
-      uint64_t ws[1] = {uint64_t(g.Cin) * 2};
+      uint64_t wd[2] = {uint64_t(tKtot), uint64_t(kTailN3)};
+      uint64_t ws[1] = {uint64_t(tKtot) * 2};
       uint32_t wb[2] = {64, uint32_t(kTailN3)};
       uint32_t we[2] = {1, 1};
       tok = encode(&pl->tmW, dt, 2, w_packed, wd, ws, wb, we, false, tmsg);
@@ -1757,7 +1771,7 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       uint32_t we[2] = {1, 1};
       tok = encode(&pl->tmW1, dt, 2, e.tail_w, wd, ws, wb, we, false, tmsg);
     }
-    if (tok) tok = encode_act(&pl->tmRes, dt, e.residual, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, tmsg);
+    if (tok) tok = encode_act(&pl->tmRes, dt, e.residual ? e.residual : e.out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, tmsg);
     if (tok) tok = encode_act(&pl->tmOut, dt, e.out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, tmsg);
     if (tok) tok = encode_act(&pl->tmOut1, dt, e.tail_out, g.B, g.Ho, g.Wo, e.tail_cout, bw, bh, bn, 1, tmsg);
     if (!tok) { delete pl; return failmsg(tmsg); }
@@ -1886,13 +1900,15 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     const bool deep = !(denv2 && denv2[0] == '0') && p.has_out && !p.has_res && !p.has_act && g.Cin >= 512 &&
                       g.Cout % kWideN == 0 && deep_tiles >= 2L * sm_count();
     if (!(wenv && wenv[0] == '0') && !stem_mode && !p.has_pre && g.kh == 1 && g.kw == 1 && g.pad == 0 && g.Cout % kWideN == 0 &&
-        (p.has_res || deep || (wide_all && (p.has_act || g.Cout > g.Cin)))) {
+        (p.has_res || deep || e.in_b || (wide_all && (p.has_act || g.Cout > g.Cin)))) {
       WideParams& wp = pl->wp;
       std::memset(&wp, 0, sizeof wp);
       pl->wide = 1; pl->kb = 128;
       int bw = 1, bh = 1, bn = 1;
       choose_patch(g.B, g.Ho, g.Wo, bw, bh, bn);
-      wp.cblks = g.Cin / 64; wp.num_k_iters = wp.cblks; wp.kw = 1; wp.stride = g.stride; wp.pad = 0;
+      const int Ktot = g.Cin + (e.in_b ? e.in_b_cin : 0);
+      wp.cblks = g.Cin / 64; wp.k1_iters = wp.cblks; wp.num_k_iters = Ktot / 64; wp.kw = 1; wp.stride = g.stride; wp.pad = 0;
+      wp.stride_b = e.in_b ? e.in_b_stride : 1;
       wp.bw = bw; wp.bh = bh; wp.bn = bn;
       wp.tiles_w = (g.Wo + bw - 1) / bw; wp.tiles_h = (g.Ho + bh - 1) / bh;
       wp.m_tiles = wp.tiles_w * wp.tiles_h * ((g.B + bn - 1) / bn);
@@ -1913,8 +1929,8 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       const bool bstat_ok = !(benv && benv[0] == '0') && !deep;
       int N = kWideN;
       wp.b_stationary = 0;
-      if (bstat_ok && g.Cin <= 128) wp.b_stationary = 1;
-      else if (bstat_ok && g.Cin == 256 && g.Cout % 128 == 0) { wp.b_stationary = 1; N = 128; }
+      if (bstat_ok && Ktot <= 128) wp.b_stationary = 1;
+      else if (bstat_ok && Ktot == 256 && g.Cout % 128 == 0) { wp.b_stationary = 1; N = 128; }
       pl->block_n = N;
       wp.n_tiles = g.Cout / N;
       const char* senv = std::getenv("B200RN_WIDE_STAGES");
@@ -1939,9 +1955,18 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
                        uint32_t((use_r ? wp.r_slots : 0) + (p.has_act ? wp.c_slots : 0)) * kChunkBytes;
       std::string wmsg;
       bool wok = encode_act(&pl->tmA, dt, in, g.B, g.H, g.W, g.Cin, bw, bh, bn, g.stride, wmsg);
+      if (wok && e.in_b) {
+        if (e.in_b_cin % 64 || e.in_b_stride < 1 || (e.in_b_h - 1) / e.in_b_stride + 1 != g.Ho || (e.in_b_w - 1) / e.in_b_stride + 1 != g.Wo) {
+          delete pl;
+          return failmsg("two-input conv: the second input must have 64-multiple channels and map onto the output grid at its stride");
+        }
+        wok = encode_act(&pl->tmA2, dt, e.in_b, g.B, e.in_b_h, e.in_b_w, e.in_b_cin, bw, bh, bn, e.in_b_stride, wmsg);
+      } else {
+        pl->tmA2 = pl->tmA;
+      }
       if (wok) {
-        uint64_t wd[2] = {uint64_t(g.Cin), uint64_t(g.Cout)};
-        uint64_t ws[1] = {uint64_t(g.Cin) * 2};
+        uint64_t wd[2] = {uint64_t(Ktot), uint64_t(g.Cout)};
+        uint64_t ws[1] = {uint64_t(Ktot) * 2};
         uint32_t wb[2] = {64, uint32_t(N)};
         uint32_t we[2] = {1, 1};
         wok = encode(&pl->tmW, dt, 2, w_packed, wd, ws, wb, we, false, wmsg);
@@ -1958,6 +1983,7 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       return pl;
     }
   }
+  if (e.in_b) { delete pl; return failmsg("two-input conv needs a 1x1 / pad-0 conv with 256-multiple output channels (conv_wide_kernel / conv_tail_kernel)"); }
   plan_geometry(*pl);
   const int bw = p.bw, bh = p.bh, bn = p.bn;
   {

@@ -24,6 +24,7 @@ constexpr int kWideThreads = (4 + kWideEpiWarps) * 32;   // operand TMA, MMA, st
 
 struct WideParams {
   int num_k_iters, cblks, kw, stride, pad;
+  int k1_iters, stride_b;      // two-input conv: K blocks [0, k1_iters) come from tmA, the rest from tmA2 at stride_b
   int bw, bh, bn, tiles_w, tiles_h, m_tiles, n_tiles;
   int stages, r_slots, c_slots, b_stationary;
   int has_res, has_out, has_act, relu, act_relu;
@@ -46,9 +47,9 @@ __device__ __forceinline__ WideTile wide_decode(const WideParams& p, int mt) {
 
 template <typename T, int N>
 __global__ void __launch_bounds__(kWideThreads, 1)
-conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-                 const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
-                 const __grid_constant__ CUtensorMap tmAct, const WideParams p) {
+conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
+                 const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmRes,
+                 const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmAct, const WideParams p) {
   constexpr int kChunks = N / 64;
   constexpr uint32_t A_BYTES = kTileM * 128;
   constexpr uint32_t B_BYTES = N * 128;
@@ -87,6 +88,7 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA); prefetch_tmap(&tmW);
+    if (p.k1_iters < p.num_k_iters) prefetch_tmap(&tmA2);
     if (p.has_res) prefetch_tmap(&tmRes);
     if (p.has_out) prefetch_tmap(&tmOut);
     if (p.has_act) prefetch_tmap(&tmAct);
@@ -131,9 +133,13 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint32_t fb = smem_u32(&full_bar[stage]);
           mbar_expect_tx(fb, p.b_stationary ? p.a_bytes : p.a_bytes + B_BYTES);
           const uint32_t a_dst = smem_u32(pipe + stage * STAGE_BYTES);
-          const int tap = it / p.cblks, cb = it - tap * p.cblks;
-          const int ky = tap / p.kw, kx = tap - ky * p.kw;
-          tma_load_4d(a_dst, &tmA, fb, cb * 64, tc.w0 * p.stride - p.pad + kx, tc.h0 * p.stride - p.pad + ky, tc.n0);
+          if (it < p.k1_iters) {
+            const int tap = it / p.cblks, cb = it - tap * p.cblks;
+            const int ky = tap / p.kw, kx = tap - ky * p.kw;
+            tma_load_4d(a_dst, &tmA, fb, cb * 64, tc.w0 * p.stride - p.pad + kx, tc.h0 * p.stride - p.pad + ky, tc.n0);
+          } else {                         // second input of a two-input 1x1 conv
+            tma_load_4d(a_dst, &tmA2, fb, (it - p.k1_iters) * 64, tc.w0 * p.stride_b, tc.h0 * p.stride_b, tc.n0);
+          }
           if (!p.b_stationary) tma_load_2d(a_dst + A_BYTES, &tmW, fb, it * 64, col0);
           if (++stage == S) { stage = 0; phase ^= 1; }
         }

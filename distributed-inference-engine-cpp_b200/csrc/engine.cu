@@ -52,6 +52,12 @@ bool tail_enabled() {
   return !(v && v[0] == '0');
 }
 
+// Two-input conv fusion of projection blocks (plan.h): on unless B200RN_DUAL_INPUT=0; tensor-core modes only.
+bool dual_input_enabled() {
+  const char* v = std::getenv("B200RN_DUAL_INPUT");
+  return !(v && v[0] == '0');
+}
+
 // FC on the tensor cores in the 16-bit modes (B200RN_FC_UMMA=0: the fp32 CUDA-core kernel, as in exact mode).
 bool fc_umma_enabled() {
   const char* v = std::getenv("B200RN_FC_UMMA");
@@ -199,7 +205,8 @@ struct b200rn {
 
   void build(const std::string& path) {
     OnnxModel model = load_onnx(path);
-    plan = build_plan(model, dt == DType::F32 ? 4 : 8, prologue_enabled(), dt != DType::F32 && tail_enabled());
+    plan = build_plan(model, dt == DType::F32 ? 4 : 8, prologue_enabled(), dt != DType::F32 && tail_enabled(),
+                      dt != DType::F32 && dual_input_enabled());
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&s_h2d, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&s_compute, cudaStreamNonBlocking));
@@ -219,7 +226,7 @@ struct b200rn {
         const bool fast_conv = L.kind == LayerKind::Conv && dt != DType::F32;
         if (fast_conv) {
           const PlanTensor& in = plan.tensors[size_t(L.in)];
-          ConvGeom g{1, in.H, in.W, L.Cin, 0, 0, L.Cout, L.kh, L.kw, L.stride, L.pad};
+          ConvGeom g{1, in.H, in.W, L.Cin + L.Cin_b, 0, 0, L.Cout, L.kh, L.kw, L.stride, L.pad};   // weights span both inputs
           D.stem = (plan.layers[size_t(in.def_layer)].kind == LayerKind::InputXform && in.Cpad == 4) ? 1 : 0;
           if (D.stem) {
             // 2 = dedicated stem7x7_kernel (one input patch per tile); 1 = generic kernel over a 5-D overlapping view
@@ -337,6 +344,11 @@ struct b200rn {
         ConvGeom g = geom(L, B);
         e.residual = tptr(L.in2);
         e.pre_scale = D.pre_scale; e.pre_shift = D.pre_shift; e.pre_relu = L.pre_relu;
+        if (L.in_b >= 0) {
+          if (!D.umma) throw ArgFail{fmt("layer '%s': a two-input conv only exists on the tensor-core path", L.name.c_str())};
+          const PlanTensor& tb = plan.tensors[size_t(L.in_b)];
+          e.in_b = tptr(L.in_b); e.in_b_cin = L.Cin_b; e.in_b_h = tb.H; e.in_b_w = tb.W; e.in_b_stride = L.stride_b;
+        }
         if (L.tail_out >= 0) {
           if (!D.umma) throw ArgFail{fmt("layer '%s': a fused tail conv only exists on the tensor-core path", L.name.c_str())};
           e.tail_w = D.tail_w; e.tail_bias = D.tail_bias; e.tail_out = out_ptr(L.tail_out);
@@ -665,7 +677,8 @@ int64_t b200rn_describe_plan(const char* onnx_path, int mode, char* buf, size_t 
   std::string text;
   int rc = guarded(nullptr, [&] {
     OnnxModel m = load_onnx(onnx_path);
-    Plan p = build_plan(m, mode == B200RN_MODE_EXACT ? 4 : 8, prologue_enabled(), mode != B200RN_MODE_EXACT && tail_enabled());
+    Plan p = build_plan(m, mode == B200RN_MODE_EXACT ? 4 : 8, prologue_enabled(), mode != B200RN_MODE_EXACT && tail_enabled(),
+                        mode != B200RN_MODE_EXACT && dual_input_enabled());
     text = p.describe();
   });
   if (rc != B200RN_OK) return -1;
@@ -721,7 +734,7 @@ int b200rn_profile_layers(b200rn_t* h, const float* d_nchw, size_t batch, int it
       if (flops) flops[li] = 2.0 * L.macs_per_sample * double(batch);
       if (bytes) {
         double b = h->dl[size_t(li)].weight_bytes;
-        for (int t : {L.in, L.in2, L.out, L.out_act, L.tail_out})
+        for (int t : {L.in, L.in2, L.in_b, L.out, L.out_act, L.tail_out})
           if (t >= 0) {
             const PlanTensor& T = h->plan.tensors[size_t(t)];
             b += double(T.elems_per_sample()) * double(batch) * double(h->elsize(T));

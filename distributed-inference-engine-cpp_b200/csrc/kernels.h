@@ -38,6 +38,11 @@ struct Epilogue {
   void* tail_out = nullptr;
   int tail_cout = 0;
   int tail_relu = 0;
+  // Second input (tensor-core path, 1x1 / pad-0 convs on conv_wide_kernel / conv_tail_kernel only): the GEMM's K runs
+  // over g.Cin channels of `in` and then in_b_cin channels of in_b, an NHWC tensor [B, in_b_h, in_b_w, in_b_cin] read
+  // at stride in_b_stride (output pixel (y, x) <- in_b pixel (y*s, x*s)); the weights are [Cout][g.Cin + in_b_cin].
+  const void* in_b = nullptr;
+  int in_b_cin = 0, in_b_h = 0, in_b_w = 0, in_b_stride = 1;
   // fp32 row output (tensor-core path, 1x1 spatial outputs only: the FC as a 1x1 conv over pooled rows):
   //   out_f32[image][c] = acc + bias[c] for c < out_f32_cols, row pitch out_f32_ld floats; no 16-bit output then.
   float* out_f32 = nullptr;

@@ -42,6 +42,7 @@ struct Builder {
   int align;
   bool consumer_prologue = true;
   bool tail_fusion = false;
+  bool dual_input = false;
   std::map<std::string, PendingPrologue> prologues;   // activated value name -> how to make it on the fly
   Plan plan;
   std::map<std::string, std::vector<int>> consumers;  // value name -> node indices
@@ -306,6 +307,55 @@ struct Builder {
     int ta = tensor_of(n.inputs[0], n), tb = tensor_of(n.inputs[1], n);
     const PlanTensor A = plan.tensors[size_t(ta)], B = plan.tensors[size_t(tb)];
     if (A.C != B.C || A.H != B.H || A.W != B.W || A.vec_f32 != B.vec_f32) fail("Add '" + n.name + "': shapes differ (broadcast is not supported)");
+    // Both operands are linear 1x1 convs read only by this Add: one GEMM over both inputs' channels.
+    if (dual_input && ta != tb) {
+      int li[2] = {-1, -1};
+      for (int side = 0; side < 2; ++side) {
+        const int t = side ? tb : ta;
+        const std::string& vname = n.inputs[size_t(side)];
+        auto pit = producer_layer.find(t);
+        if (pit == producer_layer.end()) continue;
+        const PlanLayer& P = layers[size_t(pit->second)];
+        if (P.kind != LayerKind::Conv || P.out != t || P.in2 >= 0 || P.in_b >= 0 || P.out_act >= 0 || P.relu) continue;
+        if (P.kh != 1 || P.kw != 1 || P.pad != 0 || !P.pre_scale.empty() || P.Cin % 64 || P.Cout % 256) continue;
+        if (graph_outputs.count(vname) || consumers[vname].size() != 1) continue;
+        li[side] = pit->second;
+      }
+      if (li[0] >= 0 && li[1] >= 0 && layers[size_t(li[0])].Cout == layers[size_t(li[1])].Cout) {
+        // the carrier is a stride-1 conv (its geometry is the output's); prefer the one with fewer MACs
+        int carrier = -1;
+        for (int side = 0; side < 2; ++side) {
+          const PlanLayer& P = layers[size_t(li[side])];
+          if (P.stride != 1) continue;
+          if (carrier < 0 || P.macs_per_sample < layers[size_t(carrier)].macs_per_sample) carrier = li[side];
+        }
+        if (carrier >= 0) {
+          const int other_li = carrier == li[0] ? li[1] : li[0];
+          PlanLayer& Cc = layers[size_t(carrier)];
+          PlanLayer& O = layers[size_t(other_li)];
+          const int K1 = Cc.Cin, K2 = O.Cin, Co = Cc.Cout;
+          std::vector<float> wcat(size_t(Co) * size_t(K1 + K2));
+          for (int o = 0; o < Co; ++o) {
+            std::copy(Cc.weight.begin() + size_t(o) * K1, Cc.weight.begin() + size_t(o + 1) * K1, wcat.begin() + size_t(o) * (K1 + K2));
+            std::copy(O.weight.begin() + size_t(o) * K2, O.weight.begin() + size_t(o + 1) * K2, wcat.begin() + size_t(o) * (K1 + K2) + K1);
+          }
+          Cc.weight = std::move(wcat);
+          for (int o = 0; o < Co; ++o) Cc.bias[size_t(o)] += O.bias[size_t(o)];
+          Cc.in_b = O.in; Cc.Cin_b = K2; Cc.stride_b = O.stride;
+          Cc.macs_per_sample += O.macs_per_sample;
+          Cc.name += "+" + O.name + "+" + n.name;
+          plan.tensors[size_t(Cc.out)].name = n.outputs[0];
+          value[n.outputs[0]] = Cc.out;
+          producer_layer.erase(O.out);
+          // drop the absorbed conv from the execution order and run the carrier last (both inputs exist by then)
+          order.erase(std::find(order.begin(), order.end(), other_li));
+          order.erase(std::find(order.begin(), order.end(), carrier));
+          order.push_back(carrier);
+          O.weight.clear();
+          return;
+        }
+      }
+    }
     // fuse into the Conv that produced one operand, if this Add is that operand's only reader.  When both sides
     // qualify (first block of a stage: main-branch 1x1 conv vs projection shortcut) the one with fewer MACs carries
     // the residual epilogue -- that epilogue is the expensive part of such a layer, and the smaller reduction keeps
@@ -482,13 +532,13 @@ struct Builder {
     auto& Ls = plan.layers;
     for (size_t i = 0; i < Ls.size(); ++i) {
       PlanLayer& L = Ls[i];
-      if (L.kind != LayerKind::Conv || L.out < 0 || L.out_act < 0 || L.in2 < 0 || L.tail_out >= 0) continue;
+      if (L.kind != LayerKind::Conv || L.out < 0 || L.out_act < 0 || (L.in2 < 0 && L.in_b < 0) || L.tail_out >= 0) continue;
       if (L.kh != 1 || L.kw != 1 || L.stride != 1 || L.pad != 0 || !L.pre_scale.empty()) continue;
-      if (L.Cout != 256 || L.Cin != 64) continue;
+      if (L.Cout != 256 || L.Cin != 64 || (L.in_b >= 0 && (L.Cin_b != 64 || L.in2 >= 0))) continue;
       if (L.out_act == value_or(plan.output_name)) continue;
       int readers = 0, j = -1;
       for (size_t k = 0; k < Ls.size(); ++k)
-        for (int t : {Ls[k].in, Ls[k].in2})
+        for (int t : {Ls[k].in, Ls[k].in2, Ls[k].in_b})
           if (t == L.out_act) { ++readers; j = int(k); }
       if (readers != 1 || j <= int(i)) continue;
       PlanLayer& M = Ls[size_t(j)];
@@ -529,7 +579,7 @@ struct Builder {
     // liveness + dependency check
     for (size_t i = 0; i < plan.layers.size(); ++i) {
       PlanLayer& L = plan.layers[i];
-      for (int t : {L.in, L.in2}) {
+      for (int t : {L.in, L.in2, L.in_b}) {
         if (t < 0) continue;
         PlanTensor& T = plan.tensors[size_t(t)];
         if (T.def_layer < 0) fail("internal: layer '" + L.name + "' reads '" + T.name + "' before it is produced");
@@ -567,9 +617,10 @@ struct Builder {
 
 }  // namespace
 
-Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue, bool tail_fusion) {
+Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue, bool tail_fusion, bool dual_input) {
   Builder b(model, channel_align, consumer_prologue);
   b.tail_fusion = tail_fusion;
+  b.dual_input = dual_input;
   return b.run();
 }
 
@@ -588,6 +639,7 @@ std::string Plan::describe() const {
     const PlanLayer& L = layers[i];
     os << i << " " << layer_kind_name(L.kind) << " in=" << tn(L.in) << " in2=" << tn(L.in2) << " out=" << tn(L.out)
        << " out_act=" << tn(L.out_act);
+    if (L.in_b >= 0) os << " in_b=" << tn(L.in_b) << " cin_b=" << L.Cin_b << " stride_b=" << L.stride_b;
     if (L.tail_out >= 0) os << " tail_out=" << tn(L.tail_out) << " tail_cout=" << L.tail_Cout;
     if (L.kind == LayerKind::Conv)
       os << " k=" << L.kh << "x" << L.kw << " s=" << L.stride << " p=" << L.pad << " cin=" << L.Cin << " cout=" << L.Cout;

@@ -6,6 +6,7 @@
 // Fusions are decided from the graph (consumer counts), never from layer names:
 //   Conv -> BN            (BN the only consumer)      : folded into weights + bias
 //   ... -> ReLU           (only consumer)             : epilogue ReLU
+//   Conv1x1 + Conv1x1 -> Add (projection block)        : (dual_input) one conv over both inputs' channels
 //   ... -> Add(x, other)  (only consumer)             : epilogue residual add; when both operands come from such
 //                                                       convs (projection block) the one with fewer MACs takes it
 //   T -> BN -> ReLU -> 1x1 convs only              : applied to those convs' A operand while it is
@@ -45,6 +46,7 @@ struct PlanLayer {
   std::string name;        // ONNX node names fused into this launch, '+'-joined
   int in = -1;             // main input tensor
   int in2 = -1;            // residual operand (Conv) / second operand (Add)
+  int in_b = -1;           // Conv: a second 1x1 conv summed into the same accumulator (projection shortcut), see below
   int out = -1;            // primary output (-1 when only the activated copy is kept)
   int out_act = -1;        // relu?(act_scale * primary + act_shift)
   // Conv / Gemm
@@ -60,6 +62,10 @@ struct PlanLayer {
   // activated copy of the tensor is never written to memory)
   std::vector<float> pre_scale, pre_shift;
   bool pre_relu = false;
+  // Two-input conv (dual_input fusion): out = conv1x1(in, W[:, :Cin]) + conv1x1_stride_b(in_b, W[:, Cin:]) + bias.
+  // A projection block's "main-branch 1x1 conv + shortcut 1x1 conv -> Add" is one GEMM whose K runs over both
+  // inputs' channels, so the shortcut tensor is never written or read.  weight is [Cout][Cin + Cin_b], kh = kw = 1.
+  int Cin_b = 0, stride_b = 1;
   // Conv tail: the 1x1 / stride-1 / pad-0 conv that was the only reader of this layer's activated output, run
   // inside the same launch on the activated tile while it is still in shared memory.  out_act is then -1
   // (act_scale / act_shift / act_relu still describe the activation between the two convs) and
@@ -93,6 +99,9 @@ struct Plan {
 // tail_fusion: fuse "Conv(1x1, Cin 64 -> 256 channels, + residual) -> BN -> ReLU -> Conv 1x1 (<= 128 channels)"
 // pairs -- the end of one bottleneck block and the start of the next -- into one launch when that second conv
 // is the activated tensor's only reader (tensor-core modes only: the shapes are what conv_tail_kernel takes).
-Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue = false, bool tail_fusion = false);
+// dual_input: fuse "Conv1x1(a) + Conv1x1(b) -> Add" (both linear, both only read by the Add, 64-multiple input
+// channels, 256-multiple output channels) into one two-input conv (tensor-core modes only).
+Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue = false, bool tail_fusion = false,
+                bool dual_input = false);
 
 }  // namespace rn

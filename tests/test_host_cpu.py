@@ -68,6 +68,7 @@ def test_missing_or_malformed_model_is_an_error(tmp_path):
 def test_plan_resnet50(r50_model, prologue, monkeypatch):
     monkeypatch.setenv("B200RN_PROLOGUE", "1" if prologue else "0")
     monkeypatch.setenv("B200RN_TAIL", "0")
+    monkeypatch.setenv("B200RN_DUAL_INPUT", "0")
     text = pkg.describe_plan(r50_model, "fp16")
     lines = text.strip().splitlines()
     head, layers = lines[0], lines[1:]
@@ -95,9 +96,10 @@ def test_plan_resnet50(r50_model, prologue, monkeypatch):
 
 
 def test_plan_resnet50_tail_fusion(r50_model, monkeypatch):
-    """Default 16-bit plan: at 56x56 the wide 1x1 conv (+residual) that ends a block and the narrow 1x1 conv that
-    starts the next run as one launch; the exact (fp32 CUDA-core) plan is never fused that way."""
+    """16-bit plan with tail fusion only: at 56x56 the wide 1x1 conv (+residual) that ends a block and the narrow 1x1
+    conv that starts the next run as one launch; the exact (fp32 CUDA-core) plan is never fused that way."""
     monkeypatch.delenv("B200RN_TAIL", raising=False)
+    monkeypatch.setenv("B200RN_DUAL_INPUT", "0")
     monkeypatch.setenv("B200RN_PROLOGUE", "0")
     lines = pkg.describe_plan(r50_model, "fp16").strip().splitlines()
     head, layers = lines[0], lines[1:]
@@ -109,7 +111,29 @@ def test_plan_resnet50_tail_fusion(r50_model, monkeypatch):
         assert re.search(r"in=t\d+\[64x56x56\]", l) and re.search(r"tail_out=t\d+\[64x56x56\]", l)
         assert "stage1_conv" in l and l.count("_conv") == 2       # two ONNX Conv nodes in one launch
     exact = pkg.describe_plan(r50_model, "exact").strip().splitlines()[1:]
-    assert len(exact) == 57 and not any("tail_out" in l for l in exact)
+    assert len(exact) == 57 and not any("tail_out" in l or "in_b=t" in l for l in exact)
+
+
+def test_plan_resnet50_default_16bit(r50_model, monkeypatch):
+    """Default 16-bit plan: the four projection blocks run 'main 1x1 conv + shortcut 1x1 conv + Add' as one two-input
+    conv (the shortcut tensor is never materialised), on top of the tail fusion: 51 launches for 53 convs."""
+    for v in ("B200RN_TAIL", "B200RN_DUAL_INPUT", "B200RN_PROLOGUE"):
+        monkeypatch.delenv(v, raising=False)
+    lines = pkg.describe_plan(r50_model, "fp16").strip().splitlines()
+    head, layers = lines[0], lines[1:]
+    assert "macs/sample=4089184256" in head and len(layers) == 51
+    two = [l for l in layers if "in_b=t" in l]
+    assert len(two) == 4
+    want = [("64", "64", "1", "56"), ("128", "256", "2", "28"), ("256", "512", "2", "14"), ("512", "1024", "2", "7")]
+    got = [(re.search(r" cin=(\d+) ", l).group(1), re.search(r"cin_b=(\d+)", l).group(1), re.search(r"stride_b=(\d)", l).group(1),
+            re.search(r"out=t\d+\[\d+x(\d+)x", l).group(1)) for l in two]
+    assert got == want
+    for l in two:
+        assert "in2=-" in l and "k=1x1 s=1 p=0" in l and "out_act=t" not in l.split("tail_out")[0] or "tail_out=t" in l or "out_act=t" in l
+        assert l.count("_conv") >= 2 and "_plus0" in l
+    assert sum("in2=t" in l for l in layers) == 12                  # the other residual adds stay epilogue adds
+    tails = [l for l in layers if "tail_out=t" in l]
+    assert len(tails) == 2 and sum("in_b=t" in l for l in tails) == 1   # stage 1's projection block also carries the tail
 
 
 def test_cpp_parser_matches_python_reader(tiny_model):
