@@ -1636,6 +1636,15 @@ static cudaError_t launch_tail(const UmmaConvPlan* pl, cudaStream_t s) {
   return launch_pdl(kern, pl->grid, kTailThreads, pl->smem_bytes, s, pl->tmA, pl->tmA2, pl->tmW, pl->tmW1, pl->tmRes, pl->tmOut, pl->tmOut1, pl->tp);
 }
 
+// Two-input wide layers with this many K blocks or more (streamed operands, no residual to prefetch) take three
+// operand stages and two slots per staging ring: their main loop, not the epilogue, sets the pace.  Measured:
+// stage-2/3/4 projection blocks 0.165 -> 0.134, 0.132 -> 0.101, 0.126 -> 0.093 ms; the K = 512 residual layers of
+// stage 4 lose 10 % with three stages and keep two.  (B200RN_WIDE_S3_MINK; 0 = never)
+static int wide_s3_min_k() {
+  static const int v = [] { const char* e = std::getenv("B200RN_WIDE_S3_MINK"); int k = e ? std::atoi(e) : 6; return k <= 0 ? 1 << 30 : k; }();
+  return v;
+}
+
 template <typename T, int N>
 static cudaError_t launch_wide(const UmmaConvPlan* pl, cudaStream_t s) {
   auto kern = conv_wide_kernel<T, N>;
@@ -1937,7 +1946,8 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       const uint32_t slab = wp.b_stationary ? uint32_t(wp.num_k_iters) * uint32_t(N) * 128u : 0u;
       const uint32_t stage_bytes = wp.b_stationary ? uint32_t(kTileM) * 128u : uint32_t(kTileM + N) * 128u;
       wp.stages = senv ? std::max(2, std::min(4, std::atoi(senv)))
-                       : (wp.b_stationary ? std::max(2, std::min(4, wp.num_k_iters + 1)) : ((deep && !p.has_res) ? 4 : 2));
+                       : (wp.b_stationary ? std::max(2, std::min(4, wp.num_k_iters + 1))
+                                           : ((deep && !p.has_res) ? 4 : ((e.in_b && wp.num_k_iters >= wide_s3_min_k()) ? 3 : 2)));
       const uint32_t fixed = 1024u + (p.has_act ? 3u : 1u) * uint32_t(N) * 4 + 8u * (2 * 4 + 4 + 33) + 64;
       const int slots = (int(227u * 1024) - int(fixed) - int(slab) - int(uint32_t(wp.stages) * stage_bytes)) / int(kChunkBytes);
       const bool use_r = p.has_res || p.has_out;
