@@ -61,6 +61,8 @@ _sig("b200rn_conv2d", C.c_int, [C.c_int, _vp, C.c_int, C.c_int, C.c_int, C.c_int
                                 C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _fp, _fp, C.c_int, _fp, _fp, C.c_int])
 _sig("b200rn_conv1x1_tail", C.c_int, [C.c_int, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _fp, _fp, C.c_int, _vp, _vp, _fp, _fp,
                                       C.c_int, _fp, _fp, C.c_int, C.c_int, _vp])
+_sig("b200rn_conv1x1_two_input", C.c_int, [C.c_int, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, C.c_int, C.c_int, C.c_int, C.c_int,
+                                           _fp, _fp, C.c_int, _vp, _vp, _fp, _fp, C.c_int])
 _sig("b200rn_stem_conv", C.c_int, [C.c_int, _vp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp, C.c_int, C.c_int, _vp])
 _sig("b200rn_stem_conv_static", C.c_int, [C.c_int, _vp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp, C.c_int, C.c_int, _vp,
                                           C.c_char_p, C.c_size_t])

@@ -878,6 +878,48 @@ int b200rn_conv1x1_tail(int dtype, const void* d_in, int B, int H, int W, int Ci
   });
 }
 
+int b200rn_conv1x1_two_input(int dtype, const void* d_in, int B, int H, int W, int Cin, const void* d_in_b, int Hb, int Wb,
+                             int Cin_b, int stride_b, const float* w, const float* bias, int Cout, void* d_out,
+                             void* d_out_act, const float* act_scale, const float* act_shift, int act_relu) {
+  if (!d_in || !d_in_b || !w || (!d_out && !d_out_act) || dtype < 1 || dtype > 2 || stride_b < 1) {
+    g_error = "b200rn_conv1x1_two_input: bad argument";
+    return B200RN_ERR_ARG;
+  }
+  return guarded(nullptr, [&] {
+    DType dt = DType(dtype);
+    ConvGeom g{B, H, W, Cin, H, W, Cout, 1, 1, 1, 0};
+    ConvGeom wg{B, H, W, Cin + Cin_b, H, W, Cout, 1, 1, 1, 0};       // the weights span both inputs
+    std::vector<float> hb(size_t(Cout), 0.f), hs(size_t(Cout), 1.f), ht(size_t(Cout), 0.f);
+    if (bias) hb.assign(bias, bias + Cout);
+    if (act_scale) hs.assign(act_scale, act_scale + Cout);
+    if (act_shift) ht.assign(act_shift, act_shift + Cout);
+    struct Bufs {
+      void* p[4] = {nullptr, nullptr, nullptr, nullptr};
+      ~Bufs() { for (void* q : p) cudaFree(q); }
+    } bufs;
+    bufs.p[0] = upload(hb); bufs.p[1] = upload(hs); bufs.p[2] = upload(ht);
+    size_t bytes = umma_weight_bytes(wg, 0);
+    std::vector<uint8_t> packed(bytes);
+    umma_pack_weights(w, wg, dt, 0, packed.data());
+    CK(cudaMalloc(&bufs.p[3], bytes));
+    CK(cudaMemcpy(bufs.p[3], packed.data(), bytes, cudaMemcpyHostToDevice));
+    Epilogue e;
+    e.bias = static_cast<float*>(bufs.p[0]); e.act_scale = static_cast<float*>(bufs.p[1]); e.act_shift = static_cast<float*>(bufs.p[2]);
+    e.act_relu = act_relu; e.out = d_out; e.out_act = d_out_act;
+    e.in_b = d_in_b; e.in_b_cin = Cin_b; e.in_b_h = Hb; e.in_b_w = Wb; e.in_b_stride = stride_b;
+    char msg[512] = {0};
+    UmmaConvPlan* up = umma_conv_plan_create(dt, g, d_in, bufs.p[3], e, 0, msg, sizeof msg);
+    if (!up) throw CudaFail{std::string("b200rn_conv1x1_two_input: ") + msg};
+    cudaError_t le = launch_conv_umma(up, 0);
+    cudaError_t se = cudaDeviceSynchronize();
+    umma_conv_plan_destroy(up);
+    unsigned int flag = 0;
+    if (se == cudaSuccess) se = umma_take_timeout_flag(&flag);
+    if (le != cudaSuccess || se != cudaSuccess || flag)
+      throw CudaFail{fmt("b200rn_conv1x1_two_input: launch %s / sync %s / barrier timeout %u", cudaGetErrorString(le), cudaGetErrorString(se), flag)};
+  });
+}
+
 int b200rn_stem_conv(int dtype, const float* d_in_nchw, int B, int H, int W, const float* in_scale,
                      const float* in_shift, const float* w, const float* bias, int Cout, int relu, void* d_out) {
   if (!d_in_nchw || !w || !d_out || dtype < 1 || dtype > 2) { g_error = "b200rn_stem_conv: bad argument"; return B200RN_ERR_ARG; }

@@ -139,6 +139,15 @@ int b200rn_conv2d(int dtype, const void* d_in, int B, int H, int W, int Cin, con
 int b200rn_conv1x1_tail(int dtype, const void* d_in, int B, int H, int W, int Cin, const float* w, const float* bias, int relu,
                         const void* d_residual, void* d_out, const float* act_scale, const float* act_shift, int act_relu,
                         const float* tail_w, const float* tail_bias, int tail_cout, int tail_relu, void* d_tail_out);
+/* Two-input 1x1 conv (tensor-core dtypes 1 / 2 only; the planner's fusion of a projection block's "main conv +
+ * shortcut conv -> Add", csrc/plan.h): replaces two ORT Conv nodes and the Add between them.
+ *   d_out     = conv1x1(d_in, w[:, :Cin]) + conv1x1_stride_b(d_in_b, w[:, Cin:]) + bias      [B,H,W,Cout]
+ *   d_out_act = relu?(act_scale * d_out + act_shift)                                          (optional)
+ * d_in is [B,H,W,Cin], d_in_b is [B,Hb,Wb,Cin_b] read at (y*stride_b, x*stride_b) with (Hb-1)/stride_b+1 == H (same
+ * for W); w: fp32 host [Cout][Cin + Cin_b]; Cin, Cin_b multiples of 64, Cout a multiple of 256. */
+int b200rn_conv1x1_two_input(int dtype, const void* d_in, int B, int H, int W, int Cin, const void* d_in_b, int Hb, int Wb,
+                             int Cin_b, int stride_b, const float* w, const float* bias, int Cout, void* d_out,
+                             void* d_out_act, const float* act_scale, const float* act_shift, int act_relu);
 /* Same, for the 7x7/2 stem through the tensor-core path: d_in_nchw is fp32 NCHW [B,3,H,W]; the
  * input re-layout (with per-channel scale/shift) and the conv run back to back. */
 int b200rn_stem_conv(int dtype, const float* d_in_nchw, int B, int H, int W, const float* in_scale,

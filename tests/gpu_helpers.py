@@ -131,6 +131,51 @@ def tail_case(dtype, B, H, W, tail_cout=64, relu=0, act_relu=1, tail_relu=1, see
     return out
 
 
+def two_input_case(dtype, B, H, W, Cin, Cin_b, stride_b, Cout=256, Hb=None, Wb=None, want_out=True, want_act=True, seed=0):
+    """Runs b200rn_conv1x1_two_input (main 1x1 conv + strided shortcut 1x1 conv summed in one GEMM) on random data;
+    compares with a float64 CPU evaluation of the two convs on the same rounded operands."""
+    g = torch.Generator().manual_seed(seed)
+    tdt = TORCH_DT[dtype]
+    Hb = Hb if Hb is not None else (H - 1) * stride_b + 1
+    Wb = Wb if Wb is not None else (W - 1) * stride_b + 1
+    x = torch.randn(B, Cin, H, W, generator=g).to(tdt)
+    xb = torch.randn(B, Cin_b, Hb, Wb, generator=g).to(tdt)
+    w1 = (torch.randn(Cout, Cin, 1, 1, generator=g) * (1.0 / Cin) ** 0.5).to(tdt)
+    w2 = (torch.randn(Cout, Cin_b, 1, 1, generator=g) * (1.0 / Cin_b) ** 0.5).to(tdt)
+    bias = torch.randn(Cout, generator=g) * 0.5
+    s2 = torch.rand(Cout, generator=g) + 0.5
+    t2 = torch.randn(Cout, generator=g) * 0.3
+    y = F.conv2d(x.double(), w1.double()) + F.conv2d(xb.double(), w2.double(), stride=stride_b) + bias.double().view(1, -1, 1, 1)
+    ya = (y * s2.double().view(1, -1, 1, 1) + t2.double().view(1, -1, 1, 1)).clamp_min(0)
+    d_x = x.permute(0, 2, 3, 1).contiguous().cuda()
+    d_xb = xb.permute(0, 2, 3, 1).contiguous().cuda()
+    d_out = torch.full((B, H, W, Cout), float("nan"), dtype=tdt, device="cuda") if want_out else None
+    d_act = torch.full((B, H, W, Cout), float("nan"), dtype=tdt, device="cuda") if want_act else None
+    f32 = lambda t: np.ascontiguousarray(t.float().numpy().astype(np.float32))
+    wcat = np.ascontiguousarray(np.concatenate([f32(w1.view(Cout, Cin)), f32(w2.view(Cout, Cin_b))], axis=1))
+    torch.cuda.synchronize()
+    rc = lib.b200rn_conv1x1_two_input(dtype, d_x.data_ptr(), B, H, W, Cin, d_xb.data_ptr(), Hb, Wb, Cin_b, stride_b, pkg.fptr(wcat),
+                                      pkg.fptr(f32(bias)), Cout, d_out.data_ptr() if want_out else None,
+                                      d_act.data_ptr() if want_act else None, pkg.fptr(f32(s2)), pkg.fptr(f32(t2)), 1)
+    out = {"rc": rc, "msg": lib.b200rn_global_error().decode() if rc else ""}
+    if rc:
+        return out
+    rtol, atol = TOL[dtype]
+
+    def cmp(dev, ref):
+        got = dev.float().cpu().permute(0, 3, 1, 2).double()
+        bad = ~torch.isfinite(got)
+        err = (got - ref).abs()
+        lim = atol + rtol * ref.abs()
+        return {"max_err": float(err[~bad].max()) if (~bad).any() else float("nan"), "nonfinite": int(bad.sum()),
+                "viol": int((err > lim).sum() + bad.sum()), "n": got.numel()}
+    if want_out:
+        out["out"] = cmp(d_out, y)
+    if want_act:
+        out["act"] = cmp(d_act, ya)
+    return out
+
+
 def stem_case(dtype, B, H, W, Cout=64, seed=0):
     g = torch.Generator().manual_seed(seed)
     tdt = TORCH_DT[dtype]

@@ -57,6 +57,38 @@ def test_conv1x1_tail_rejects_unsupported_shapes():
     assert rc != 0 and b"tail" in gh.lib.b200rn_global_error()
 
 
+TWO_INPUT_CASES = [
+    # (B, H, W, Cin, Cin_b, stride_b, Cout): the four projection blocks of ResNet-50 at small batch, then ragged / odd
+    # shapes: a patch that does not fill the tile, an even second input (last row / column unused), many N tiles
+    (4, 56, 56, 64, 64, 1, 256), (6, 28, 28, 128, 256, 2, 512), (9, 14, 14, 256, 512, 2, 1024), (20, 7, 7, 512, 1024, 2, 2048),
+    (3, 13, 9, 64, 128, 1, 256), (2, 5, 7, 128, 64, 2, 256), (1, 3, 3, 64, 64, 3, 512),
+]
+
+
+@pytest.mark.parametrize("dtype", [1, 2], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("case", TWO_INPUT_CASES, ids=["%dx%dx%d_%d+%ds%d_%d" % c for c in TWO_INPUT_CASES])
+def test_conv1x1_two_input(dtype, case):
+    B, H, W, Cin, Cin_b, sb, Cout = case
+    r = gh.two_input_case(dtype, B, H, W, Cin, Cin_b, sb, Cout=Cout)
+    assert r["rc"] == 0, r["msg"]
+    assert r["out"]["viol"] == 0, r["out"]
+    assert r["act"]["viol"] == 0, r["act"]
+
+
+def test_conv1x1_two_input_even_second_input_and_bad_geometry():
+    # Hb = 2*H: the shortcut's last row and column are never read (as 56 -> 28 in the network)
+    r = gh.two_input_case(2, 2, 6, 6, 64, 64, 2, Hb=12, Wb=12, want_act=False)
+    assert r["rc"] == 0 and r["out"]["viol"] == 0, r
+    import numpy as np
+    x = torch.zeros(1, 6, 6, 64, dtype=torch.float16, device="cuda")
+    xb = torch.zeros(1, 10, 10, 64, dtype=torch.float16, device="cuda")     # 10 at stride 2 gives 5, not the 6x6 output grid
+    o = torch.zeros(1, 6, 6, 256, dtype=torch.float16, device="cuda")
+    w = np.zeros((256, 128), dtype=np.float32)
+    rc = gh.lib.b200rn_conv1x1_two_input(2, x.data_ptr(), 1, 6, 6, 64, xb.data_ptr(), 10, 10, 64, 2, gh.pkg.fptr(w), None, 256,
+                                         o.data_ptr(), None, None, None, 0)
+    assert rc != 0 and b"second input" in gh.lib.b200rn_global_error()
+
+
 def test_conv2d_rejects_bad_shapes():
     # the tensor-core path needs channel multiples of 64; it must say so rather than fall back
     x = torch.zeros(1, 8, 8, 32, dtype=torch.float16, device="cuda")
