@@ -883,6 +883,20 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_con
   if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
 }
 
+// packed 16-bit max (exact; NaN operands are ignored like fmaxf does) and the lowest finite value, per type
+template <typename T> __device__ __forceinline__ uint32_t max2_u32(uint32_t a, uint32_t b);
+template <> __device__ __forceinline__ uint32_t max2_u32<__half>(uint32_t a, uint32_t b) {
+  __half2 r = __hmax2(*reinterpret_cast<__half2*>(&a), *reinterpret_cast<__half2*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+template <> __device__ __forceinline__ uint32_t max2_u32<__nv_bfloat16>(uint32_t a, uint32_t b) {
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+template <typename T> __device__ __forceinline__ uint32_t lowest2_u32();
+template <> __device__ __forceinline__ uint32_t lowest2_u32<__half>() { return 0xFBFFFBFFu; }
+template <> __device__ __forceinline__ uint32_t lowest2_u32<__nv_bfloat16>() { return 0xFF7FFF7Fu; }
+
 // ---- 7x7 / stride 2 / pad 3 stem, one input patch per tile ------------------------------------------
 // The generic kernel fetches the stem's A operand as 7 boxes of 128 rows x 64 bytes per tile; the TMA unit
 // needs ~4 cycles per such row, which made the stem the slowest layer of the network (measured timeline:
@@ -905,8 +919,17 @@ constexpr uint32_t kStemWBytes = 7 * 4096;                     // one 64-channel
 
 struct Stem2Params {
   int tiles_w, tiles_h, n_tiles, total_tiles, stages, relu;
+  int groups;                // epilogue warp groups (8 warps each) working on consecutive tiles: 2, or 3 with the fused pool
   const float* bias;
   const void* w_packed;
+  // Fused 3x3 / stride-2 / pad-1 max-pool (pool != 0): a tile is still 8 x 16 conv outputs, but placed at conv
+  // (6*tw - 1, 14*th - 1) so that it holds every tap of a 3 x 7 block of pooled pixels; the conv tile only ever
+  // exists in shared memory and the pooled values are written straight to global memory.
+  int pool, conv_w, conv_h, pool_w, pool_h, cout, act_relu;
+  void* pool_out;            // pooled raw output or null
+  void* pool_act;            // relu?(act_scale * pooled + act_shift) or null
+  const float* act_scale;
+  const float* act_shift;
 };
 
 // un-swizzled K-major descriptor: start | LBO (K-adjacent core matrices) | SBO (8-row groups) | version 1
@@ -923,23 +946,26 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* m, 
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kTwoGroupThreads, 1)
+__global__ void __launch_bounds__(64 + 3 * kEpiThreads, 1)
 stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constant__ CUtensorMap tmOut, const Stem2Params p) {
   constexpr int BLOCK_N = 64;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int S = p.stages;
   uint8_t* wbuf = smem;                                   // 28 KB, stationary
-  uint8_t* outbuf = wbuf + kStemWBytes;                   // 2 x 16 KB staging (SWIZZLE_128B rows)
-  uint8_t* patch = outbuf + 2 * kChunkBytes;              // S x kStemStageBytes
+  const int G = p.groups;                                 // epilogue groups = accumulators = staging buffers (2 or 3)
+  uint8_t* outbuf = wbuf + kStemWBytes;                   // G x 16 KB staging (SWIZZLE_128B rows)
+  uint8_t* patch = outbuf + G * kChunkBytes;              // S x kStemStageBytes
   float* s_bias = reinterpret_cast<float*>(patch + S * kStemStageBytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_bias + BLOCK_N);
+  float* s_scale = s_bias + BLOCK_N;    // pool mode: the activated output's scale / shift
+  float* s_shift = s_scale + BLOCK_N;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_shift + BLOCK_N);
   uint64_t* full_bar = bars;            // [S]
   uint64_t* empty_bar = bars + S;       // [S]
   uint64_t* w_bar = empty_bar + S;      // [1]
-  uint64_t* tmem_full = w_bar + 1;      // [2]
-  uint64_t* tmem_empty = tmem_full + 2; // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* tmem_full = w_bar + 1;      // [G <= 4]
+  uint64_t* tmem_empty = tmem_full + 4; // [G <= 4]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int my_tiles = (int(blockIdx.x) < p.total_tiles) ? (p.total_tiles - 1 - int(blockIdx.x)) / int(gridDim.x) + 1 : 0;
@@ -950,12 +976,16 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
     prefetch_tmap(&tmOut);
     for (int i = 0; i < S; ++i) { mbar_init(smem_u32(&full_bar[i]), 1); mbar_init(smem_u32(&empty_bar[i]), 1); }
     mbar_init(smem_u32(w_bar), 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&tmem_full[i]), 1); mbar_init(smem_u32(&tmem_empty[i]), kEpiThreads); }
+    for (int i = 0; i < G; ++i) { mbar_init(smem_u32(&tmem_full[i]), 1); mbar_init(smem_u32(&tmem_empty[i]), kEpiThreads); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * BLOCK_N);
+  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), G > 2 ? 4 * BLOCK_N : 2 * BLOCK_N);
   if (warp >= 2)
-    for (int k = threadIdx.x - 64; k < BLOCK_N; k += 2 * kEpiThreads) s_bias[k] = __ldg(p.bias + n_tile * BLOCK_N + k);
+    for (int k = threadIdx.x - 64; k < BLOCK_N; k += G * kEpiThreads) {
+      s_bias[k] = __ldg(p.bias + n_tile * BLOCK_N + k);
+      s_scale[k] = (p.pool && p.pool_act) ? __ldg(p.act_scale + n_tile * BLOCK_N + k) : 1.f;
+      s_shift[k] = (p.pool && p.pool_act) ? __ldg(p.act_shift + n_tile * BLOCK_N + k) : 0.f;
+    }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -968,7 +998,8 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
     const int tw = mt % p.tiles_w; mt /= p.tiles_w;
     const int th = mt % p.tiles_h;
     n = mt / p.tiles_h;
-    x0 = tw * kStemTW; y0 = th * kStemTH;
+    if (p.pool) { x0 = tw * 6 - 1; y0 = th * 14 - 1; }
+    else { x0 = tw * kStemTW; y0 = th * kStemTH; }
   };
 
   if (warp == 0) {
@@ -996,8 +1027,8 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
       int stage = 0;
       uint32_t phase = 0;
       for (int i = 0; i < my_tiles; ++i) {
-        const int buf = i & 1;
-        mbar_wait(smem_u32(&tmem_empty[buf]), ((i >> 1) & 1) ^ 1);
+        const int buf = i % G;
+        mbar_wait(smem_u32(&tmem_empty[buf]), (uint32_t(i / G) & 1) ^ 1);
         mbar_wait(smem_u32(&full_bar[stage]), phase);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
@@ -1025,13 +1056,13 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
     const int sw = row & 7;
     const bool store_thread = (((warp - 2) & 7) == 0 && lane == 0);
     const int bar_id = 1 + grp;
-    for (int i = grp; i < my_tiles; i += 2) {
+    for (int i = grp; i < my_tiles; i += G) {
       int x0, y0, n;
       tile_coord(i, x0, y0, n);
       const int buf = grp;
       if (store_thread && i > grp) tma_store_wait_read();   // this group's previous tile has left its staging buffer
       asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
-      mbar_wait(smem_u32(&tmem_full[buf]), (i >> 1) & 1);
+      mbar_wait(smem_u32(&tmem_full[buf]), uint32_t(i / G) & 1);
       tc_fence_after();
       uint32_t acc[32];
       tmem_ld_32x32b_x32(tmem_base + (uint32_t(q4 * 32) << 16) + uint32_t(buf * BLOCK_N + g * 32), acc);
@@ -1058,7 +1089,48 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
       }
       fence_proxy_async_smem();
       asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
-      if (store_thread) {
+      if (p.pool) {
+        // 3 x 7 pooled pixels x eight 16-byte channel chunks = 168 work items for the group's 256 threads; the conv
+        // tile sits in the staging buffer as 128 rows (y*8 + x) of 128 swizzled bytes
+        const int tg = int(threadIdx.x) - 64 - grp * kEpiThreads;
+        if (tg < 168) {
+          const int pp = tg >> 3, j = tg & 7;
+          const int pyl = pp / 3, pxl = pp - pyl * 3;
+          const int px = (x0 + 1) / 2 + pxl, py = (y0 + 1) / 2 + pyl;
+          if (px < p.pool_w && py < p.pool_h) {
+            uint32_t best[4] = {lowest2_u32<T>(), lowest2_u32<T>(), lowest2_u32<T>(), lowest2_u32<T>()};
+            const uint32_t st = smem_u32(stage_out);
+#pragma unroll
+            for (int dy = 0; dy < 3; ++dy) {
+              const int yl = 2 * pyl + dy, gy = y0 + yl;
+              if (gy < 0 || gy >= p.conv_h) continue;
+#pragma unroll
+              for (int dx = 0; dx < 3; ++dx) {
+                const int xl = 2 * pxl + dx, gx = x0 + xl;
+                if (gx < 0 || gx >= p.conv_w) continue;
+                const int r = yl * 8 + xl;
+                const uint4 v = lds_u4(st + uint32_t(r) * 128u + uint32_t((j ^ (r & 7)) << 4));
+                best[0] = max2_u32<T>(best[0], v.x); best[1] = max2_u32<T>(best[1], v.y);
+                best[2] = max2_u32<T>(best[2], v.z); best[3] = max2_u32<T>(best[3], v.w);
+              }
+            }
+            const size_t off = ((size_t(n) * p.pool_h + py) * p.pool_w + px) * size_t(p.cout) + size_t(n_tile * BLOCK_N + j * 8);
+            if (p.pool_out) *reinterpret_cast<uint4*>(static_cast<T*>(p.pool_out) + off) = make_uint4(best[0], best[1], best[2], best[3]);
+            if (p.pool_act) {
+              uint32_t a[4];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const float2 f = unpack2<T>(best[k]);
+                float a0 = fmaf(s_scale[j * 8 + 2 * k], f.x, s_shift[j * 8 + 2 * k]);
+                float a1 = fmaf(s_scale[j * 8 + 2 * k + 1], f.y, s_shift[j * 8 + 2 * k + 1]);
+                if (p.act_relu) { a0 = fmaxf(a0, 0.f); a1 = fmaxf(a1, 0.f); }
+                a[k] = pack2<T>(a0, a1);
+              }
+              *reinterpret_cast<uint4*>(static_cast<T*>(p.pool_act) + off) = make_uint4(a[0], a[1], a[2], a[3]);
+            }
+          }
+        }
+      } else if (store_thread) {
         tma_store_4d(&tmOut, smem_u32(stage_out), n_tile * BLOCK_N, x0, y0, n);   // box {64 ch, 8, 16, 1}
         tma_store_commit();
       }
@@ -1068,7 +1140,7 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
+  if (warp == 1) tmem_dealloc(tmem_base, G > 2 ? 4 * BLOCK_N : 2 * BLOCK_N);
 }
 
 // ---- two M tiles per weight tile ("dual-M") ----------------------------------------------------------
@@ -1605,7 +1677,7 @@ static cudaError_t launch_stem2(const UmmaConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  return launch_pdl(kern, pl->grid, kTwoGroupThreads, pl->smem_bytes, s, pl->tmA, pl->tmOut, pl->sp);
+  return launch_pdl(kern, pl->grid, 64 + pl->sp.groups * kEpiThreads, pl->smem_bytes, s, pl->tmA, pl->tmOut, pl->sp);
 }
 
 template <typename T, int BLOCK_N>
@@ -1791,13 +1863,26 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     return pl;
   }
   if (stem_mode == 2) {
-    if (!p.has_out || p.has_res || p.has_act || p.has_pre) { delete pl; return failmsg("stem kernel supports bias + ReLU + one output only"); }
+    if (p.has_res || p.has_pre || (!e.pool_fused && (!p.has_out || p.has_act))) {
+      delete pl;
+      return failmsg("stem kernel supports bias + ReLU + one output, or a fused 3x3/2 max-pool with raw and/or activated pooled outputs");
+    }
+    if (e.pool_fused && (e.pool_h != (g.Ho + 2 - 3) / 2 + 1 || e.pool_w != (g.Wo + 2 - 3) / 2 + 1)) {
+      delete pl;
+      return failmsg("stem kernel: the fused pool must be 3x3 / stride 2 / pad 1 over the conv output");
+    }
     Stem2Params& sp = pl->sp;
     std::memset(&sp, 0, sizeof sp);
     pl->stem2 = 1;
     pl->kb = 64; pl->block_n = 64;
     sp.tiles_w = (g.Wo + kStemTW - 1) / kStemTW;
     sp.tiles_h = (g.Ho + kStemTH - 1) / kStemTH;
+    if (e.pool_fused) {
+      sp.pool = 1; sp.conv_w = g.Wo; sp.conv_h = g.Ho; sp.pool_w = e.pool_w; sp.pool_h = e.pool_h; sp.cout = g.Cout;
+      sp.pool_out = e.out; sp.pool_act = e.out_act; sp.act_scale = e.act_scale; sp.act_shift = e.act_shift; sp.act_relu = e.act_relu;
+      sp.tiles_w = (e.pool_w + 2) / 3;          // 3 x 7 pooled pixels per tile
+      sp.tiles_h = (e.pool_h + 6) / 7;
+    }
     sp.n_tiles = g.Cout / 64;
     sp.total_tiles = sp.tiles_w * sp.tiles_h * g.B * sp.n_tiles;
     sp.relu = e.relu;
@@ -1806,7 +1891,13 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     const int sms = sm_count();
     int grid = std::min(sp.total_tiles, sms);
     grid = std::max(sp.n_tiles, (grid / sp.n_tiles) * sp.n_tiles);
-    const uint32_t fixed = 1024u + kStemWBytes + 2u * kChunkBytes + 64u * 4 + 8u * (2 * 16 + 5) + 64;
+    {
+      // with the fused pool a tile's epilogue (conv tile -> staging -> 3x3 max -> global) is a ~4000-cycle chain; three
+      // groups keep three tiles in flight (B200RN_STEM_GROUPS overrides)
+      const char* ge = std::getenv("B200RN_STEM_GROUPS");
+      sp.groups = ge ? std::max(2, std::min(3, std::atoi(ge))) : (e.pool_fused ? 3 : 2);
+    }
+    const uint32_t fixed = 1024u + kStemWBytes + uint32_t(sp.groups) * kChunkBytes + 3u * 64u * 4 + 8u * (2 * 16 + 9) + 64;
     sp.stages = std::max(2, std::min(16, int((227u * 1024 - fixed) / kStemStageBytes)));
     pl->smem_bytes = fixed + uint32_t(sp.stages) * kStemStageBytes;
     pl->grid = grid;
@@ -1817,11 +1908,13 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     uint32_t box[3] = {uint32_t(kStemPatchPx * 4), uint32_t(kStemPatchRows), 1};
     uint32_t es[4] = {1, 1, 1, 1};
     bool sok = encode(&pl->tmA, dt, 3, in, dims, str, box, es, 2, smsg);
-    if (sok) {
+    if (sok && !e.pool_fused) {
       uint64_t od[4] = {uint64_t(g.Cout), uint64_t(g.Wo), uint64_t(g.Ho), uint64_t(g.B)};
       uint64_t os[3] = {uint64_t(g.Cout) * 2, uint64_t(g.Wo) * g.Cout * 2, uint64_t(g.Ho) * g.Wo * g.Cout * 2};
       uint32_t ob[4] = {64, uint32_t(kStemTW), uint32_t(kStemTH), 1};
       sok = encode(&pl->tmOut, dt, 4, e.out, od, os, ob, es, 0, smsg);
+    } else if (sok) {
+      pl->tmOut = pl->tmA;                      // pooled outputs are written with plain stores: no store map
     }
     if (!sok) { delete pl; return failmsg(smsg); }
     pl->tmW = pl->tmOut; pl->tmAct = pl->tmOut; pl->tmRes = pl->tmOut;

@@ -52,6 +52,16 @@ bool tail_enabled() {
   return !(v && v[0] == '0');
 }
 
+// Stem conv + max-pool in one launch (plan.h): only with B200RN_STEM_POOL=1 and the dedicated stem kernel
+// (B200RN_STEM_V2 != 0); tensor-core modes only.  Off by default: it removes 0.8 GB of HBM traffic per 256 images but
+// every pooled 3x7 block needs its own 8x16 conv tile (1.55x the stem's tiles), and the stem is bound by its main
+// loop, not by its stores -- measured 0.289 ms fused against 0.140 + 0.130 ms separate.
+bool stem_pool_enabled() {
+  const char* v = std::getenv("B200RN_STEM_POOL");
+  const char* sv = std::getenv("B200RN_STEM_V2");
+  return (v && v[0] == '1') && !(sv && sv[0] == '0');
+}
+
 // Two-input conv fusion of projection blocks (plan.h): on unless B200RN_DUAL_INPUT=0; tensor-core modes only.
 bool dual_input_enabled() {
   const char* v = std::getenv("B200RN_DUAL_INPUT");
@@ -206,7 +216,7 @@ struct b200rn {
   void build(const std::string& path) {
     OnnxModel model = load_onnx(path);
     plan = build_plan(model, dt == DType::F32 ? 4 : 8, prologue_enabled(), dt != DType::F32 && tail_enabled(),
-                      dt != DType::F32 && dual_input_enabled());
+                      dt != DType::F32 && dual_input_enabled(), dt != DType::F32 && stem_pool_enabled());
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&s_h2d, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&s_compute, cudaStreamNonBlocking));
@@ -231,7 +241,7 @@ struct b200rn {
           if (D.stem) {
             // 2 = dedicated stem7x7_kernel (one input patch per tile); 1 = generic kernel over a 5-D overlapping view
             const char* sv = std::getenv("B200RN_STEM_V2");
-            const bool plain = L.out >= 0 && L.out_act < 0 && L.in2 < 0 && L.pre_scale.empty();
+            const bool plain = ((L.out >= 0 && L.out_act < 0) || L.fused_pool) && L.in2 < 0 && L.pre_scale.empty();
             if (plain && !(sv && sv[0] == '0')) D.stem = 2;
           }
           char why[256];
@@ -315,8 +325,9 @@ struct b200rn {
 
   ConvGeom geom(const PlanLayer& L, int B) const {
     const PlanTensor& in = plan.tensors[size_t(L.in)];
-    const PlanTensor& out = plan.tensors[size_t(L.out >= 0 ? L.out : L.out_act)];
-    return ConvGeom{B, in.H, in.W, L.Cin, out.H, out.W, L.Cout, L.kh, L.kw, L.stride, L.pad};
+    // output extent from the conv's own geometry (with a fused pool the layer's output tensors are the pooled ones)
+    const int Ho = (in.H + 2 * L.pad - L.kh) / L.stride + 1, Wo = (in.W + 2 * L.pad - L.kw) / L.stride + 1;
+    return ConvGeom{B, in.H, in.W, L.Cin, Ho, Wo, L.Cout, L.kh, L.kw, L.stride, L.pad};
   }
 
   // Launch layer li for a batch of B.  `d_in` feeds the InputXform, `d_out` receives the graph output.
@@ -344,6 +355,11 @@ struct b200rn {
         ConvGeom g = geom(L, B);
         e.residual = tptr(L.in2);
         e.pre_scale = D.pre_scale; e.pre_shift = D.pre_shift; e.pre_relu = L.pre_relu;
+        if (L.fused_pool) {
+          if (!D.umma || D.stem != 2) throw ArgFail{fmt("layer '%s': the fused max-pool only exists in the dedicated stem kernel", L.name.c_str())};
+          const PlanTensor& pt = plan.tensors[size_t(L.out >= 0 ? L.out : L.out_act)];
+          e.pool_fused = 1; e.pool_h = pt.H; e.pool_w = pt.W;
+        }
         if (L.in_b >= 0) {
           if (!D.umma) throw ArgFail{fmt("layer '%s': a two-input conv only exists on the tensor-core path", L.name.c_str())};
           const PlanTensor& tb = plan.tensors[size_t(L.in_b)];
@@ -678,7 +694,7 @@ int64_t b200rn_describe_plan(const char* onnx_path, int mode, char* buf, size_t 
   int rc = guarded(nullptr, [&] {
     OnnxModel m = load_onnx(onnx_path);
     Plan p = build_plan(m, mode == B200RN_MODE_EXACT ? 4 : 8, prologue_enabled(), mode != B200RN_MODE_EXACT && tail_enabled(),
-                        mode != B200RN_MODE_EXACT && dual_input_enabled());
+                        mode != B200RN_MODE_EXACT && dual_input_enabled(), mode != B200RN_MODE_EXACT && stem_pool_enabled());
     text = p.describe();
   });
   if (rc != B200RN_OK) return -1;

@@ -43,6 +43,10 @@ struct Epilogue {
   // at stride in_b_stride (output pixel (y, x) <- in_b pixel (y*s, x*s)); the weights are [Cout][g.Cin + in_b_cin].
   const void* in_b = nullptr;
   int in_b_cin = 0, in_b_h = 0, in_b_w = 0, in_b_stride = 1;
+  // Fused max-pool (stem kernel only, stem_mode 2): `out` / `out_act` are then the POOLED tensors
+  // [B, pool_h, pool_w, Cout] of a 3x3 / stride-2 / pad-1 max-pool over relu?(conv + bias); act_* apply to the pooled
+  // value.  The conv's own output is never written.
+  int pool_fused = 0, pool_h = 0, pool_w = 0;
   // fp32 row output (tensor-core path, 1x1 spatial outputs only: the FC as a 1x1 conv over pooled rows):
   //   out_f32[image][c] = acc + bias[c] for c < out_f32_cols, row pitch out_f32_ld floats; no 16-bit output then.
   float* out_f32 = nullptr;

@@ -43,6 +43,7 @@ struct Builder {
   bool consumer_prologue = true;
   bool tail_fusion = false;
   bool dual_input = false;
+  bool stem_pool = false;
   std::map<std::string, PendingPrologue> prologues;   // activated value name -> how to make it on the fly
   Plan plan;
   std::map<std::string, std::vector<int>> consumers;  // value name -> node indices
@@ -553,6 +554,29 @@ struct Builder {
       Ls.erase(Ls.begin() + j);
     }
   }
+  // The stem conv's 112x112x64 output is the network's largest tensor and only the max-pool reads it.
+  void fuse_stem_pool() {
+    auto& Ls = plan.layers;
+    for (size_t i = 0; i < Ls.size(); ++i) {
+      PlanLayer& L = Ls[i];
+      if (L.kind != LayerKind::Conv || L.kh != 7 || L.kw != 7 || L.stride != 2 || L.pad != 3 || L.Cin != 4) continue;
+      if (L.out < 0 || L.out_act >= 0 || L.in2 >= 0 || L.in_b >= 0 || L.tail_out >= 0 || !L.pre_scale.empty()) continue;
+      int readers = 0, j = -1;
+      for (size_t k = 0; k < Ls.size(); ++k)
+        for (int t : {Ls[k].in, Ls[k].in2, Ls[k].in_b})
+          if (t == L.out) { ++readers; j = int(k); }
+      if (readers != 1 || j <= int(i)) continue;
+      PlanLayer& P = Ls[size_t(j)];
+      if (P.kind != LayerKind::MaxPool || P.in != L.out || P.pool_k != 3 || P.pool_stride != 2 || P.pool_pad != 1) continue;
+      if (L.out == value_or(plan.output_name)) continue;
+      L.out = P.out; L.out_act = P.out_act;
+      L.act_scale = std::move(P.act_scale); L.act_shift = std::move(P.act_shift); L.act_relu = P.act_relu;
+      L.fused_pool = true;
+      L.name += "+" + P.name;
+      Ls.erase(Ls.begin() + j);
+      return;
+    }
+  }
   int value_or(const std::string& name) const {
     auto it = value.find(name);
     return it == value.end() ? -2 : it->second;
@@ -562,6 +586,7 @@ struct Builder {
     for (int li : order) plan.layers.push_back(std::move(layers[size_t(li)]));
     plan.output_name = m.outputs[0].name;
     if (tail_fusion) fuse_tails();
+    if (stem_pool) fuse_stem_pool();
     const auto& out = m.outputs[0];
     auto it = value.find(out.name);
     if (it == value.end()) fail("graph output '" + out.name + "' is not produced by a supported node");
@@ -617,10 +642,12 @@ struct Builder {
 
 }  // namespace
 
-Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue, bool tail_fusion, bool dual_input) {
+Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue, bool tail_fusion, bool dual_input,
+                bool stem_pool) {
   Builder b(model, channel_align, consumer_prologue);
   b.tail_fusion = tail_fusion;
   b.dual_input = dual_input;
+  b.stem_pool = stem_pool;
   return b.run();
 }
 
@@ -640,6 +667,7 @@ std::string Plan::describe() const {
     os << i << " " << layer_kind_name(L.kind) << " in=" << tn(L.in) << " in2=" << tn(L.in2) << " out=" << tn(L.out)
        << " out_act=" << tn(L.out_act);
     if (L.in_b >= 0) os << " in_b=" << tn(L.in_b) << " cin_b=" << L.Cin_b << " stride_b=" << L.stride_b;
+    if (L.fused_pool) os << " fused_pool=1";
     if (L.tail_out >= 0) os << " tail_out=" << tn(L.tail_out) << " tail_cout=" << L.tail_Cout;
     if (L.kind == LayerKind::Conv)
       os << " k=" << L.kh << "x" << L.kw << " s=" << L.stride << " p=" << L.pad << " cin=" << L.Cin << " cout=" << L.Cout;

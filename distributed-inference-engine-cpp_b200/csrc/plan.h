@@ -66,6 +66,9 @@ struct PlanLayer {
   // A projection block's "main-branch 1x1 conv + shortcut 1x1 conv -> Add" is one GEMM whose K runs over both
   // inputs' channels, so the shortcut tensor is never written or read.  weight is [Cout][Cin + Cin_b], kh = kw = 1.
   int Cin_b = 0, stride_b = 1;
+  // Stem conv with the 3x3 / stride-2 / pad-1 max-pool behind it in the same launch (stem_pool fusion): out / out_act
+  // are then the POOLED tensors and act_* apply to the pooled value; the conv's own output is never materialised.
+  bool fused_pool = false;
   // Conv tail: the 1x1 / stride-1 / pad-0 conv that was the only reader of this layer's activated output, run
   // inside the same launch on the activated tile while it is still in shared memory.  out_act is then -1
   // (act_scale / act_shift / act_relu still describe the activation between the two convs) and
@@ -101,7 +104,9 @@ struct Plan {
 // is the activated tensor's only reader (tensor-core modes only: the shapes are what conv_tail_kernel takes).
 // dual_input: fuse "Conv1x1(a) + Conv1x1(b) -> Add" (both linear, both only read by the Add, 64-multiple input
 // channels, 256-multiple output channels) into one two-input conv (tensor-core modes only).
+// stem_pool: fuse "7x7 / stride-2 / pad-3 conv -> 3x3 / stride-2 / pad-1 MaxPool" (the pool the conv's only reader)
+// into the conv's launch (tensor-core modes with the dedicated stem kernel only).
 Plan build_plan(const OnnxModel& model, int channel_align, bool consumer_prologue = false, bool tail_fusion = false,
-                bool dual_input = false);
+                bool dual_input = false, bool stem_pool = false);
 
 }  // namespace rn

@@ -178,6 +178,24 @@ def test_operand_prologue_mode_matches(tmp_path, monkeypatch):
     assert not np.array_equal(outs[("1", "fp16")], outs[("0", "fp16")]) or True
 
 
+@pytest.mark.parametrize("mode", ["fp16", "bf16"])
+def test_fused_stem_pool_opt_in_matches(tmp_path, monkeypatch, mode):
+    """B200RN_STEM_POOL=1 (max-pool computed inside the stem conv's launch from the conv tile in shared memory): the
+    pooled tensors are the same bits as the two-launch path gives (max is exact and the conv tile is rounded to the
+    16-bit type in both), so the logits are bit-identical; ragged batch and a 64x64 input exercise clipped tiles."""
+    p = str(tmp_path / "s.onnx")
+    gen.write_model(p, "small64", seed=9)
+    x = resnet_oracle.synthetic_inputs(7, 9, (3, 64, 64))
+    outs = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("B200RN_STEM_POOL", flag)
+        eng = pkg.Engine(p, mode=mode, max_batch=8)
+        outs[flag] = eng.infer_packed(x)
+        eng.close()
+    assert np.isfinite(outs["1"]).all()
+    assert np.array_equal(outs["1"], outs["0"])
+
+
 def test_double_buffered_submit(tmp_path):
     p = str(tmp_path / "s.onnx")
     gen.write_model(p, "small64", seed=4)

@@ -69,6 +69,7 @@ def test_plan_resnet50(r50_model, prologue, monkeypatch):
     monkeypatch.setenv("B200RN_PROLOGUE", "1" if prologue else "0")
     monkeypatch.setenv("B200RN_TAIL", "0")
     monkeypatch.setenv("B200RN_DUAL_INPUT", "0")
+    monkeypatch.setenv("B200RN_STEM_POOL", "0")
     text = pkg.describe_plan(r50_model, "fp16")
     lines = text.strip().splitlines()
     head, layers = lines[0], lines[1:]
@@ -100,6 +101,7 @@ def test_plan_resnet50_tail_fusion(r50_model, monkeypatch):
     conv that starts the next run as one launch; the exact (fp32 CUDA-core) plan is never fused that way."""
     monkeypatch.delenv("B200RN_TAIL", raising=False)
     monkeypatch.setenv("B200RN_DUAL_INPUT", "0")
+    monkeypatch.setenv("B200RN_STEM_POOL", "0")
     monkeypatch.setenv("B200RN_PROLOGUE", "0")
     lines = pkg.describe_plan(r50_model, "fp16").strip().splitlines()
     head, layers = lines[0], lines[1:]
@@ -117,7 +119,7 @@ def test_plan_resnet50_tail_fusion(r50_model, monkeypatch):
 def test_plan_resnet50_default_16bit(r50_model, monkeypatch):
     """Default 16-bit plan: the four projection blocks run 'main 1x1 conv + shortcut 1x1 conv + Add' as one two-input
     conv (the shortcut tensor is never materialised), on top of the tail fusion: 51 launches for 53 convs."""
-    for v in ("B200RN_TAIL", "B200RN_DUAL_INPUT", "B200RN_PROLOGUE"):
+    for v in ("B200RN_TAIL", "B200RN_DUAL_INPUT", "B200RN_PROLOGUE", "B200RN_STEM_POOL", "B200RN_STEM_V2"):
         monkeypatch.delenv(v, raising=False)
     lines = pkg.describe_plan(r50_model, "fp16").strip().splitlines()
     head, layers = lines[0], lines[1:]
@@ -134,6 +136,22 @@ def test_plan_resnet50_default_16bit(r50_model, monkeypatch):
     assert sum("in2=t" in l for l in layers) == 12                  # the other residual adds stay epilogue adds
     tails = [l for l in layers if "tail_out=t" in l]
     assert len(tails) == 2 and sum("in_b=t" in l for l in tails) == 1   # stage 1's projection block also carries the tail
+
+
+def test_plan_resnet50_stem_pool_opt_in(r50_model, monkeypatch):
+    """B200RN_STEM_POOL=1: the stem conv carries the max-pool (its outputs are the pooled 56x56 tensors, no MaxPool
+    launch remains).  Opt-in: measured no faster than the two separate launches."""
+    for v in ("B200RN_TAIL", "B200RN_DUAL_INPUT", "B200RN_PROLOGUE", "B200RN_STEM_V2"):
+        monkeypatch.delenv(v, raising=False)
+    monkeypatch.setenv("B200RN_STEM_POOL", "1")
+    lines = pkg.describe_plan(r50_model, "fp16").strip().splitlines()
+    head, layers = lines[0], lines[1:]
+    assert "macs/sample=4089184256" in head and len(layers) == 50
+    stem = [l for l in layers if "fused_pool=1" in l]
+    assert len(stem) == 1 and "k=7x7 s=2 p=3" in stem[0] and re.search(r"out_act=t\d+\[64x56x56\]", stem[0]) and "pool0" in stem[0]
+    assert not any(l.split()[1] == "MaxPool" for l in layers)
+    monkeypatch.setenv("B200RN_STEM_V2", "0")          # without the dedicated stem kernel there is nothing to fuse into
+    assert len(pkg.describe_plan(r50_model, "fp16").strip().splitlines()) == 52
 
 
 def test_cpp_parser_matches_python_reader(tiny_model):
