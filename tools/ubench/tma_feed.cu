@@ -5,6 +5,8 @@
 // One producer thread per CTA keeps a ring of `stages` (A+B) slots full; one consumer thread frees each slot the
 // moment it lands (an infinitely fast MMA).  With clusters of C CTAs (same N tile, different M tiles) each CTA
 // issues 1/C of every B box with .multicast::cluster, and a slot is reused only after all C consumers released it.
+// Single-GPU tool: A and B are cudaMalloc'd on the current device.  TMA multicast loads here read only this GPU's
+// memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 tools/ubench/tma_feed.cu -o tools/ubench/tma_feed
 #include <cuda.h>
 #include <cuda_fp16.h>
