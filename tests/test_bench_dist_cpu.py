@@ -33,3 +33,5 @@ def test_reference_arm_under_torchrun_runs_on_rank0_only():
     j = json.loads(lines[0])
     assert j["impl"] == "reference" and j["cpu_baseline"]["kind"] == "port" and j["value"] > 0
     assert j["e2e"]["h2d_bytes_per_step"] == 0 and j["unit"] == "images/s"
+    # torchrun exports OMP_NUM_THREADS=1 (2 here) to its ranks; the arm must still use every core it is allowed on
+    assert j["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))

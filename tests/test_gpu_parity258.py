@@ -1,0 +1,92 @@
+"""Network parity on the TIMED configuration: the 258-sample parity set of SURVEY.md 8(d) (256 N(0,1) images with
+seeds 0..255, an all-zeros image and the zero-padded 3-float payload of /root/reference/benchmark.py:21-24) goes
+through ONE batch_predict call on a handle created with max_batch = 256 -- the batch size bench.py times, where
+choose_patch / the N-tile cost model / the dual-M and 2-CTA item counts differ from the batch-32 tests -- and is
+compared with the fp32 CPU oracle (oracle/resnet_oracle.py, unfused restatement of what Session::Run executes,
+src/inference_engine.cpp:134-209).
+
+Bars (BASELINE.json north_star), all constants fixed here in advance:
+  exact mode   max-abs logit error <= 1e-3 and top-1 equal on all 258 samples.
+  fp16 / bf16  max-abs <= ABS_BOUND and top-1 equal on every sample whose fp64-oracle top-1/top-2 margin exceeds
+               MARGIN[mode].  MARGIN is 6*sqrt(2) x the mode's RMS logit error measured in round 1 (0.016 fp16,
+               0.125 bf16 on this fixture, logit std 2.9): the distance at which two logits with independent errors
+               of that size cannot change order.  It does NOT move with the error measured in the run.  The fp32 and
+               fp64 oracles agree on all 258 top-1 classes (tests/golden/resnet50_parity258_seed0.npz), so samples
+               below the margin are near-ties for a 16-bit implementation only; they are counted and printed
+               ("plain" agreement), and the plain agreement has its own floor.
+"""
+import os
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+import b200rn_loader  # noqa: E402
+import parity_set  # noqa: E402
+from oracle import resnet_oracle  # noqa: E402
+from tools import make_resnet50v2_onnx as gen  # noqa: E402
+
+pkg = b200rn_loader.load_package()
+
+ABS_BOUND = {"exact": 1e-3, "fp16": 0.2, "bf16": 1.5}
+MARGIN = {"exact": 0.0, "fp16": 0.15, "bf16": 1.0}
+PLAIN_FLOOR = {"exact": 258, "fp16": 245, "bf16": 200}     # of 258
+
+
+@pytest.fixture(scope="module")
+def fixture258(tmp_path_factory, golden_dir):
+    path = str(tmp_path_factory.mktemp("m") / "r50.onnx")
+    gen.write_model(path, "resnet50", seed=0)
+    xs = parity_set.samples()
+    ora = resnet_oracle.OracleEngine(path)
+    ref = []
+    for i in range(0, len(xs), 43):                      # bounded host memory: 43 images per oracle pass
+        ref.extend(ora.batch_predict(xs[i:i + 43]))
+    ref = np.stack(ref)
+    g = np.load(os.path.join(golden_dir, "resnet50_parity258_seed0.npz"))
+    # the oracle on this box says what the committed golden says (fp32 reduction order differs between hosts)
+    assert np.abs(ref[g["rows"]] - g["logits_fp32"]).max() <= 2e-3
+    assert (ref.argmax(1) == g["top1_fp64"]).all()
+    return path, xs, ref, g
+
+
+@pytest.mark.parametrize("mode", ["exact", "fp16", "bf16"])
+def test_parity258_at_max_batch_256(fixture258, mode):
+    path, xs, ref, g = fixture258
+    eng = pkg.Engine(path, mode=mode, max_batch=256)
+    out = np.stack(eng.batch_predict(xs))                # 256 + 2: one full slice and a ragged one, both slots
+    again = np.stack(eng.batch_predict(xs[:256]))        # second pass of the same handle (graph capture / replay)
+    eng.close()
+    assert out.shape == (258, 1000) and np.isfinite(out).all()
+    assert np.array_equal(again, out[:256]), "a replayed batch differs from its first (eager) run"
+    err = np.abs(out - ref).max(1)
+    agree = out.argmax(1) == ref.argmax(1)
+    margin = g["margin_fp64"]
+    decided = margin > MARGIN[mode]
+    rel = np.linalg.norm(out - ref) / np.linalg.norm(ref - ref.mean())
+    rms = float(np.sqrt(np.mean((out - ref) ** 2)))
+    wrong = np.nonzero(~agree)[0]
+    print("\n[parity258/%s] max-abs %.3e, rms %.3e, rel-L2 %.2e (logit std %.2f); plain top-1 agreement %d/258; decided "
+          "(fp64 margin > %.2f): %d, of which agree: %d; disagreeing samples (index: margin): %s"
+          % (mode, err.max(), rms, rel, ref.std(), agree.sum(), MARGIN[mode], decided.sum(), (agree & decided).sum(),
+             ", ".join("%d: %.3f" % (i, margin[i]) for i in wrong)))
+    assert err.max() <= ABS_BOUND[mode], "max-abs %.3e exceeds the %s bound %.1e (sample %d)" % (err.max(), mode, ABS_BOUND[mode], err.argmax())
+    assert agree[decided].all(), "top-1 differs on decided samples %s" % np.nonzero(~agree & decided)[0]
+    assert agree.sum() >= PLAIN_FLOOR[mode]
+
+
+def test_batch_256_equals_batch_32_slices(fixture258):
+    """The same images through a max_batch = 32 handle (other patches, tile counts and kernels per layer): within twice
+    the fp16 bound of each other and of the oracle; exact mode agrees to 1e-4."""
+    path, xs, ref, _ = fixture258
+    sub = xs[:64]
+    for mode, tol in (("exact", 1e-4), ("fp16", 2 * ABS_BOUND["fp16"])):
+        big = pkg.Engine(path, mode=mode, max_batch=256)
+        a = np.stack(big.batch_predict(sub))
+        big.close()
+        small = pkg.Engine(path, mode=mode, max_batch=32)
+        b = np.stack(small.batch_predict(sub))
+        small.close()
+        assert np.abs(a - b).max() <= tol, "%s: batch-256 and batch-32 plans differ by %g" % (mode, np.abs(a - b).max())

@@ -5,6 +5,9 @@ device pool was divided up when it started, a request thread that cannot tolerat
 synchronisation cudaMalloc implies, a plugin host that does not let plugins own device memory.  For
 them the library keeps the stem's scratch (framed input, packed filters, bias, input scale/shift) in
 one fixed device array; this test checks that the result is the same as the allocating entry point's.
+The comparison target is b200rn_stem_conv rather than the CPU oracle: that entry point is itself pinned to a
+float64 CPU convolution by tests/test_gpu_ops.py::test_stem_conv, so agreement with it carries the oracle's
+verdict over to the static variant.
 
 It lives in its own file, collected last, so a `-x` run has already exercised every other test.
 The scratch array is shared and keeps the previous call's contents, so the check is made on two calls
