@@ -452,14 +452,14 @@ def main():
     # ---- CPU baseline: bounded sample on rank 0 at N=1 ---------------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, cores, dt = cpu_baseline_run(images=32, iters=12)
+        v, cores, dt = cpu_baseline_run(images=32, iters=30)
         # second row: the reference's own thread setting (SetIntraOpNumThreads(4), src/inference_engine.cpp:19), and
         # BASELINE configs[0] (batch 1) at both thread counts -- all bounded
-        v4, c4, dt4 = cpu_baseline_run(images=32, iters=2, threads=4)
+        v4, c4, dt4 = cpu_baseline_run(images=32, iters=4, threads=4)
         v1, c1, dt1 = cpu_baseline_run(images=1, iters=12)
         v14, c14, dt14 = cpu_baseline_run(images=1, iters=8, threads=4)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": "32 images x 12 passes (%.1f s) of the same synthetic workload; torch-CPU fp32 unfused restatement "
+               "sample": "32 images x 30 passes (%.1f s) of the same synthetic workload; torch-CPU fp32 unfused restatement "
                          "(oracle/resnet_oracle.py) -- ONNX Runtime CPU is not runnable on this image" % dt,
                "rows": [{"batch": 32, "threads": cores, "images_per_s": v, "seconds": dt},
                         {"batch": 32, "threads": c4, "images_per_s": v4, "seconds": dt4,

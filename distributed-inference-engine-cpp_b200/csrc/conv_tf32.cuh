@@ -1,0 +1,276 @@
+// Exact-mode convolution on the tensor cores: fp32 activations and weights, 3 x TF32 split products accumulated in
+// fp32 tensor memory.  (included by conv_umma.cu inside namespace rn::{anonymous})
+//
+// tcgen05 has no fp32-input MMA; kind::tf32 keeps 10 mantissa bits of each operand.  Each fp32 value is therefore
+// split exactly into hi = the value with its low 13 mantissa bits cleared and lo = value - hi (again cut to TF32), and
+//     a * w  ~=  a_hi * w_hi  +  a_hi * w_lo  +  a_lo * w_hi          (the dropped a_lo * w_lo is ~2^-22 relative)
+// The weights are split once on the host ([Cout][K] hi and lo arrays).  The activation tile arrives by TMA as raw fp32
+// and four transform warps split it in shared memory (hi in place, lo into a second buffer of the same swizzled layout)
+// before the MMA thread sees the stage.  Per K step of 8 channels two instructions are issued:
+//     D[:, 0 .. 2N)   += A_hi * [W_hi ; W_lo]^T     one M128 x 2N x K8 MMA over the hi and lo weight tiles, which sit back
+//                                                   to back in shared memory: columns [0, N) collect hi*hi, [N, 2N) hi*lo
+//     D[:, N .. 2N)   += A_lo * W_hi^T              M128 x N x K8
+// so the small terms are summed among themselves and added to the large one only once, in the epilogue
+// (v = D[c] + D[N + c] + bias).  An accumulator is 2N columns; two of them fill tensor memory at N = 128.
+// Epilogue (8 warps): bias, ReLU, residual (read straight from global memory, 128 contiguous bytes per thread), raw and/or
+// BN-ReLU'd output staged in swizzled shared memory and written by TMA stores, 32 channels (128 bytes) per chunk.
+// K is ordered (ky, kx, cin) in blocks of 32 channels; the operand box is {32 ch, bw, bh, bn} fp32 with the conv's
+// stride as element stride and TMA zero fill as padding, exactly like the 16-bit kernels.
+constexpr int kT32XfWarps = 4;
+constexpr int kT32Threads = 64 + kT32XfWarps * 32 + kEpiThreads;     // TMA, MMA, 4 transform warps, 8 epilogue warps
+
+struct Tf32Params {
+  int num_k_iters, cblks, kw, stride, pad;
+  int bw, bh, bn, tiles_w, tiles_h, n_tiles, total_tiles, num_stages;
+  int has_res, has_out, has_act, relu, act_relu;
+  int cout;                       // row pitch (floats) of the residual tensor
+  int Ho, Wo, B;
+  uint32_t rows, a_bytes;
+  const float* bias;
+  const float* act_scale;
+  const float* act_shift;
+  const float* residual;          // fp32 NHWC [B, Ho, Wo, cout] or null
+};
+
+// kind::tf32 instruction descriptor: D fp32 (bit 4), A and B formats = 2 (TF32), both K-major, N >> 3, M >> 4
+template <int N>
+__device__ __forceinline__ constexpr uint32_t make_idesc_tf32() {
+  return (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(N >> 3) << 17) | (uint32_t(kTileM >> 4) << 24);
+}
+__device__ __forceinline__ void umma_tf32_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %5, 0;\n\t"
+      "mov.b64 da, {%1, %3};\n\t"
+      "mov.b64 db, {%2, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, p;\n\t"
+      "}" ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(kT32Threads, 1)
+conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmWhi,
+                   const __grid_constant__ CUtensorMap tmWlo, const __grid_constant__ CUtensorMap tmOut,
+                   const __grid_constant__ CUtensorMap tmAct, const Tf32Params p) {
+  constexpr int kChunks = BLOCK_N / 32;               // 32 fp32 channels = one 128-byte staging row
+  constexpr uint32_t A_BYTES = kTileM * 128;          // 128 rows x 32 fp32
+  constexpr uint32_t B_BYTES = BLOCK_N * 128;         // one of the two weight tiles
+  constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;   // A_hi | A_lo | W_hi | W_lo
+  constexpr uint32_t ACC_COLS = 2 * BLOCK_N;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int S = p.num_stages;
+  uint8_t* pipe = smem;
+  uint8_t* outbuf = pipe + S * STAGE_BYTES;           // raw-output staging chunk (16 KB)
+  uint8_t* actbuf = outbuf + kChunkBytes;             // activated-output staging chunk (16 KB)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(actbuf + kChunkBytes);
+  uint64_t* full_bar = bars;                  // [S]  TMA -> transform warps
+  uint64_t* xf_bar = full_bar + S;            // [S]  transform warps -> MMA (4 warp arrivals)
+  uint64_t* empty_bar = xf_bar + S;           // [S]  MMA -> TMA
+  uint64_t* tmem_full = empty_bar + S;        // [2]
+  uint64_t* tmem_empty = tmem_full + 2;       // [2]  (8 warp arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int my_tiles = (int(blockIdx.x) < p.total_tiles) ? (p.total_tiles - 1 - int(blockIdx.x)) / int(gridDim.x) + 1 : 0;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA); prefetch_tmap(&tmWhi); prefetch_tmap(&tmWlo);
+    if (p.has_out) prefetch_tmap(&tmOut);
+    if (p.has_act) prefetch_tmap(&tmAct);
+    for (int i = 0; i < S; ++i) {
+      mbar_init(smem_u32(&full_bar[i]), 1);
+      mbar_init(smem_u32(&xf_bar[i]), kT32XfWarps);
+      mbar_init(smem_u32(&empty_bar[i]), 1);
+    }
+    for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&tmem_full[i]), 1); mbar_init(smem_u32(&tmem_empty[i]), kEpiWarps); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * ACC_COLS >= 512 ? 512 : (2 * ACC_COLS));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
+
+  auto tile_coord = [&](int i, int& w0, int& h0, int& n0, int& col0) {
+    const int tile = int(blockIdx.x) + i * int(gridDim.x);
+    col0 = (tile % p.n_tiles) * BLOCK_N;
+    int mt = tile / p.n_tiles;
+    const int tw = mt % p.tiles_w; mt /= p.tiles_w;
+    const int th = mt % p.tiles_h;
+    w0 = tw * p.bw; h0 = th * p.bh; n0 = (mt / p.tiles_h) * p.bn;
+  };
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < my_tiles; ++i) {
+        int w0, h0, n0, col0;
+        tile_coord(i, w0, h0, n0, col0);
+        for (int it = 0; it < p.num_k_iters; ++it) {
+          mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
+          const uint32_t fb = smem_u32(&full_bar[stage]);
+          mbar_expect_tx(fb, p.a_bytes + 2 * B_BYTES);
+          const uint32_t dst = smem_u32(pipe + stage * STAGE_BYTES);
+          const int tap = it / p.cblks, cb = it - tap * p.cblks;
+          const int ky = tap / p.kw, kx = tap - ky * p.kw;
+          tma_load_4d(dst, &tmA, fb, cb * 32, w0 * p.stride - p.pad + kx, h0 * p.stride - p.pad + ky, n0);
+          tma_load_2d(dst + 2 * A_BYTES, &tmWhi, fb, it * 32, col0);
+          tma_load_2d(dst + 2 * A_BYTES + B_BYTES, &tmWlo, fb, it * 32, col0);
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    constexpr uint32_t idesc_wide = make_idesc_tf32<2 * BLOCK_N>();
+    constexpr uint32_t idesc_one = make_idesc_tf32<BLOCK_N>();
+    constexpr uint32_t desc_hi = smem_desc_hi<128>();
+    if (elect_one()) {
+      const uint32_t pipe_lo = smem_desc_lo(smem_u32(pipe));
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < my_tiles; ++i) {
+        const int buf = i & 1;
+        mbar_wait(smem_u32(&tmem_empty[buf]), ((uint32_t(i) >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + uint32_t(buf) * ACC_COLS;
+        for (int it = 0; it < p.num_k_iters; ++it) {
+          mbar_wait(smem_u32(&xf_bar[stage]), phase);
+          tc_fence_after();
+          const uint32_t ahi = pipe_lo + uint32_t(stage) * (STAGE_BYTES >> 4);
+          const uint32_t alo = ahi + (A_BYTES >> 4);
+          const uint32_t bhi = ahi + 2 * (A_BYTES >> 4);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {       // K = 8 fp32 = 32 bytes per instruction
+            umma_tf32_lo(tmem_d, ahi + 2 * k, bhi + 2 * k, desc_hi, idesc_wide, (it | k) != 0 ? 1u : 0u);
+            umma_tf32_lo(tmem_d + BLOCK_N, alo + 2 * k, bhi + 2 * k, desc_hi, idesc_one, 1u);
+          }
+          umma_commit(smem_u32(&empty_bar[stage]));
+          if (it == p.num_k_iters - 1) umma_commit(smem_u32(&tmem_full[buf]));
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp < 2 + kT32XfWarps) {
+    // ===== operand split: A -> A_hi (in place) and A_lo, 16 bytes per thread per step, layout-preserving =====
+    const int t = threadIdx.x - 64;                 // 0..127
+    int stage = 0;
+    uint32_t phase = 0;
+    const int total = my_tiles * p.num_k_iters;
+    for (int q = 0; q < total; ++q) {
+      mbar_wait(smem_u32(&full_bar[stage]), phase);
+      const uint32_t a_hi = smem_u32(pipe + stage * STAGE_BYTES);
+#pragma unroll
+      for (int j = 0; j < int(A_BYTES / 16 / 128); ++j) {
+        const uint32_t off = uint32_t(j * 128 + t) * 16u;
+        const float4 a = lds_f4(a_hi + off);
+        float4 h, l;
+        h.x = tf32_hi(a.x); h.y = tf32_hi(a.y); h.z = tf32_hi(a.z); h.w = tf32_hi(a.w);
+        l.x = tf32_hi(a.x - h.x); l.y = tf32_hi(a.y - h.y); l.z = tf32_hi(a.z - h.z); l.w = tf32_hi(a.w - h.w);
+        sts_u4(a_hi + off, make_uint4(__float_as_uint(h.x), __float_as_uint(h.y), __float_as_uint(h.z), __float_as_uint(h.w)));
+        sts_u4(a_hi + A_BYTES + off, make_uint4(__float_as_uint(l.x), __float_as_uint(l.y), __float_as_uint(l.z), __float_as_uint(l.w)));
+      }
+      fence_proxy_async_smem();            // generic-proxy writes -> visible to the tensor core's reads
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&xf_bar[stage]));
+      if (++stage == S) { stage = 0; phase ^= 1; }
+    }
+  } else {
+    // ===== epilogue: 8 warps; thread = one output pixel (TMEM lane) x 16 of a chunk's 32 channels =====
+    const int ew = warp - 2 - kT32XfWarps;
+    const int q4 = warp & 3;                // TMEM lane quarter this warp may access
+    const int g = ew >> 2;                  // which half of every 32-channel chunk (0/1)
+    const int row = q4 * 32 + lane;
+    const int sw = row & 7;
+    const bool store_thread = (ew == 0 && lane == 0);
+    const uint32_t lane_addr = tmem_base + (uint32_t(q4 * 32) << 16);
+    const uint32_t out_row = smem_u32(outbuf) + uint32_t(row) * 128u;
+    const uint32_t act_row = smem_u32(actbuf) + uint32_t(row) * 128u;
+    int cc = 0;
+    for (int i = 0; i < my_tiles; ++i) {
+      int w0, h0, n0, col0;
+      tile_coord(i, w0, h0, n0, col0);
+      const int buf = i & 1;
+      // this thread's output pixel (for the residual read): row -> (image, y, x) inside the patch
+      const int px = row % p.bw, py = (row / p.bw) % p.bh, pn = row / (p.bw * p.bh);
+      const int ox = w0 + px, oy = h0 + py, on = n0 + pn;
+      const bool in_range = row < int(p.rows) && ox < p.Wo && oy < p.Ho && on < p.B;
+      const float* res_px = p.residual + ((size_t(on) * p.Ho + oy) * p.Wo + ox) * size_t(p.cout);
+      mbar_wait(smem_u32(&tmem_full[buf]), (uint32_t(i) >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < kChunks; ++c, ++cc) {
+        const int ch0 = c * 32 + g * 16;            // first of this thread's 16 channels within the N tile
+        uint32_t d0[16], d1[16];
+        tmem_ld_32x32b_x16(lane_addr + uint32_t(buf) * ACC_COLS + uint32_t(ch0), d0);
+        tmem_ld_32x32b_x16(lane_addr + uint32_t(buf) * ACC_COLS + uint32_t(BLOCK_N + ch0), d1);
+        float4 bv[4], rv[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) bv[k] = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + ch0) + k);
+        if (p.has_res) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            rv[k] = in_range ? __ldg(reinterpret_cast<const float4*>(res_px + col0 + ch0) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        tmem_ld_wait();
+        if (c == kChunks - 1) {             // accumulator fully read: hand it back to the MMA thread
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&tmem_empty[buf]));
+        }
+        if (store_thread && cc > 0) tma_store_wait_read();   // the previous chunk's stores have read both staging buffers
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float v[4];
+          v[0] = __uint_as_float(d0[4 * k + 0]) + __uint_as_float(d1[4 * k + 0]) + bv[k].x;
+          v[1] = __uint_as_float(d0[4 * k + 1]) + __uint_as_float(d1[4 * k + 1]) + bv[k].y;
+          v[2] = __uint_as_float(d0[4 * k + 2]) + __uint_as_float(d1[4 * k + 2]) + bv[k].z;
+          v[3] = __uint_as_float(d0[4 * k + 3]) + __uint_as_float(d1[4 * k + 3]) + bv[k].w;
+          if (p.relu) { v[0] = fmaxf(v[0], 0.f); v[1] = fmaxf(v[1], 0.f); v[2] = fmaxf(v[2], 0.f); v[3] = fmaxf(v[3], 0.f); }
+          if (p.has_res) { v[0] += rv[k].x; v[1] += rv[k].y; v[2] += rv[k].z; v[3] += rv[k].w; }
+          const uint32_t slot16 = uint32_t(((g * 4 + k) ^ sw) << 4);      // SWIZZLE_128B: 16-byte slot XOR (row mod 8)
+          if (p.has_out)
+            sts_u4(out_row + slot16, make_uint4(__float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3])));
+          if (p.has_act) {
+            const float4 s4 = __ldg(reinterpret_cast<const float4*>(p.act_scale + col0 + ch0) + k);
+            const float4 t4 = __ldg(reinterpret_cast<const float4*>(p.act_shift + col0 + ch0) + k);
+            float a[4] = {fmaf(s4.x, v[0], t4.x), fmaf(s4.y, v[1], t4.y), fmaf(s4.z, v[2], t4.z), fmaf(s4.w, v[3], t4.w)};
+            if (p.act_relu) { a[0] = fmaxf(a[0], 0.f); a[1] = fmaxf(a[1], 0.f); a[2] = fmaxf(a[2], 0.f); a[3] = fmaxf(a[3], 0.f); }
+            sts_u4(act_row + slot16, make_uint4(__float_as_uint(a[0]), __float_as_uint(a[1]), __float_as_uint(a[2]), __float_as_uint(a[3])));
+          }
+        }
+        fence_proxy_async_smem();
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (store_thread) {
+          if (p.has_out) tma_store_4d(&tmOut, smem_u32(outbuf), col0 + c * 32, w0, h0, n0);
+          if (p.has_act) tma_store_4d(&tmAct, smem_u32(actbuf), col0 + c * 32, w0, h0, n0);
+          tma_store_commit();
+        }
+      }
+    }
+    if (store_thread) tma_store_wait_read();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * ACC_COLS >= 512 ? 512 : (2 * ACC_COLS));
+}

@@ -1342,6 +1342,7 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
 #include "conv_tail.cuh"
 #include "conv_wide.cuh"
+#include "conv_pair.cuh"
 
 // ---- host side --------------------------------------------------------------------------------
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -1414,6 +1415,8 @@ struct UmmaConvPlan {
   HaloParams hp;
   int dual = 0;           // large-K layer routed to conv_dualm_kernel (two M tiles per weight tile)
   DualParams dp;
+  int pair = 0;           // large-K layer routed to conv_pair_kernel (CTA pair, tcgen05.mma.cta_group::2, M = 256)
+  PairParams pp;
   int stem2 = 0;          // stem routed to stem7x7_kernel (tmA = patch map, tmOut = {64, 8, 16, 1} store map)
   Stem2Params sp;
   int wide = 0;           // epilogue-bound 1x1 conv with a 256-wide N tile routed to conv_wide_kernel
@@ -1602,6 +1605,24 @@ static void plan_geometry(UmmaConvPlan& pl) {
   pl.smem_bytes = fixed + uint32_t(stages) * stage_eff;
 }
 
+// CTA-pair kernel switches: B200RN_PAIR=0 keeps the single-SM kernels; B200RN_PAIR_MINK = smallest K-block count routed there
+static bool pair_enabled() {
+  const char* v = std::getenv("B200RN_PAIR");
+  return !(v && v[0] == '0');
+}
+// Measured at batch 256 (profiles/r2_pair_ab.md): with the 256-wide N tile the pair kernel wins on every large-K layer
+// (3x3 @14x14 0.062 -> 0.049 ms, 1x1 1024->256 0.043 -> 0.038), with N = 128 (Cout = 128: a CTA stages a 64-row
+// weight half per 128-row A tile, 96 B/clk/SM of L2 feed like the single-SM kernels) it loses 0.054 -> 0.067 ms, so
+// Cout % 256 != 0 layers stay on the single-SM kernels unless B200RN_PAIR=2 (tests).
+static bool pair_n_ok(int cout) {
+  const char* v = std::getenv("B200RN_PAIR");
+  return cout % 256 == 0 || (v && v[0] == '2' && cout % 128 == 0);
+}
+static int pair_min_k() {
+  const char* v = std::getenv("B200RN_PAIR_MINK");
+  return v ? std::max(1, std::atoi(v)) : 8;
+}
+
 static bool pdl_enabled() {
   static const bool on = !(std::getenv("B200RN_PDL") && std::getenv("B200RN_PDL")[0] == '0');
   return on;
@@ -1694,6 +1715,21 @@ static cudaError_t launch_dual(const UmmaConvPlan* pl, cudaStream_t s) {
   return launch_pdl(kern, pl->grid, kTwoGroupThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmOut, pl->dp);
 }
 
+template <typename T, int BLOCK_N>
+static cudaError_t launch_pair(const UmmaConvPlan* pl, cudaStream_t s) {
+  auto kern = conv_pair_kernel<T, BLOCK_N>;
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    configured_device = dev;
+  }
+  // the cluster shape (2,1,1) is part of the kernel (__cluster_dims__); the grid is a multiple of 2
+  return launch_pdl(kern, pl->grid, kPairThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmOut, pl->pp);
+}
+
 template <typename T, int N1>
 static cudaError_t launch_tail(const UmmaConvPlan* pl, cudaStream_t s) {
   auto kern = conv_tail_kernel<T, N1>;
@@ -1740,6 +1776,10 @@ cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
   if (pl->tail) {
     if (pl->tp_n1 == 64) return bf ? launch_tail<__nv_bfloat16, 64>(pl, s) : launch_tail<__half, 64>(pl, s);
     return bf ? launch_tail<__nv_bfloat16, 128>(pl, s) : launch_tail<__half, 128>(pl, s);
+  }
+  if (pl->pair) {
+    if (pl->block_n == 128) return bf ? launch_pair<__nv_bfloat16, 128>(pl, s) : launch_pair<__half, 128>(pl, s);
+    return bf ? launch_pair<__nv_bfloat16, 256>(pl, s) : launch_pair<__half, 256>(pl, s);
   }
   if (pl->dual) {
     if (pl->block_n == 128) return bf ? launch_dual<__nv_bfloat16, 128>(pl, s) : launch_dual<__half, 128>(pl, s);
@@ -1999,7 +2039,11 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     int pbw = 1, pbh = 1, pbn = 1;
     choose_patch(g.B, g.Ho, g.Wo, pbw, pbh, pbn);
     const long deep_tiles = long((g.Wo + pbw - 1) / pbw) * ((g.Ho + pbh - 1) / pbh) * ((g.B + pbn - 1) / pbn) * (g.Cout / kWideN);
-    const bool deep = !(denv2 && denv2[0] == '0') && p.has_out && !p.has_res && !p.has_act && g.Cin >= 512 &&
+    // layers the CTA-pair kernel takes (decided after plan_geometry below) do not go the "deep" way
+    const bool pair_takes = pair_enabled() && !stem_mode && p.has_out && !p.has_res && !p.has_act && !p.has_pre && !p.out_f32 &&
+                            g.kh * g.kw * (g.Cin / 64) >= pair_min_k() && pair_n_ok(g.Cout) &&
+                            long((g.Wo + pbw - 1) / pbw) * ((g.Ho + pbh - 1) / pbh) * ((g.B + pbn - 1) / pbn) >= 2 && sm_count() >= 2;
+    const bool deep = !pair_takes && !(denv2 && denv2[0] == '0') && p.has_out && !p.has_res && !p.has_act && g.Cin >= 512 &&
                       g.Cout % kWideN == 0 && deep_tiles >= 2L * sm_count();
     if (!(wenv && wenv[0] == '0') && !stem_mode && !p.has_pre && g.kh == 1 && g.kw == 1 && g.pad == 0 && g.Cout % kWideN == 0 &&
         (p.has_res || deep || e.in_b || (wide_all && (p.has_act || g.Cout > g.Cin)))) {
@@ -2090,6 +2134,30 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   plan_geometry(*pl);
   const int bw = p.bw, bh = p.bh, bn = p.bn;
   {
+    // Large-K layer with a plain epilogue: one 256 x N tile per CTA pair (conv_pair_kernel)
+    const int m_tiles = p.tiles_w * p.tiles_h * ((g.B + bn - 1) / bn);
+    const int sms = sm_count();
+    if (pair_enabled() && !stem_mode && p.has_out && !p.has_res && !p.has_act && !p.has_pre && !p.out_f32 &&
+        p.num_k_iters >= pair_min_k() && pair_n_ok(g.Cout) && m_tiles >= 2 && sms >= 2) {
+      PairParams& pp = pl->pp;
+      std::memset(&pp, 0, sizeof pp);
+      pl->pair = 1;
+      pl->block_n = (g.Cout % 256 == 0) ? 256 : 128;
+      pp.num_k_iters = p.num_k_iters; pp.cblks = p.cblks; pp.kw = p.kw; pp.stride = p.stride; pp.pad = p.pad;
+      pp.bw = bw; pp.bh = bh; pp.bn = bn; pp.tiles_w = p.tiles_w; pp.tiles_h = p.tiles_h;
+      pp.m_tiles = m_tiles; pp.n_tiles = g.Cout / pl->block_n;
+      pp.total_items = ((m_tiles + 1) / 2) * pp.n_tiles;
+      pp.relu = p.relu; pp.a_bytes = p.a_bytes; pp.bias = p.bias;
+      const uint32_t stage_bytes = uint32_t(kTileM * 128 + (pl->block_n / 2) * 128);
+      const uint32_t fixed = 1024u + 2 * kChunkBytes + 8u * (2 * 8 + 4) + 64;
+      pp.num_stages = std::max(2, std::min(8, int((227u * 1024 - fixed) / stage_bytes)));
+      pl->smem_bytes = fixed + uint32_t(pp.num_stages) * stage_bytes;
+      pl->grid = 2 * std::min(pp.total_items, sms / 2);
+      p.n_tiles = pp.n_tiles;
+      p.b_bytes = uint32_t(pl->block_n) * 128;
+    }
+  }
+  if (!pl->pair) {
     // Large-K layer with a plain epilogue: consider two M tiles per weight tile.  Same cost model as the N-tile
     // choice: (rounds over the SMs) x (bytes staged per K block) must come out lower than the single-M plan's.
     const char* denv = std::getenv("B200RN_DUALM");
@@ -2144,7 +2212,7 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       const uint64_t K = uint64_t(g.kh) * g.kw * g.Cin;
       uint64_t wd[2] = {K, uint64_t(g.Cout)};
       uint64_t ws[1] = {K * 2};
-      uint32_t wb[2] = {64, uint32_t(pl->block_n)};
+      uint32_t wb[2] = {64, uint32_t(pl->pair ? pl->block_n / 2 : pl->block_n)};   // a CTA of a pair stages half the N tile
       uint32_t we[2] = {1, 1};
       ok = encode(&pl->tmW, dt, 2, w_packed, wd, ws, wb, we, false, msg);
     }
@@ -2157,8 +2225,9 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
   if (!ok) { delete pl; return failmsg(msg); }
   if (std::getenv("B200RN_VERBOSE"))
     std::fprintf(stderr, "[b200rn] conv %dx%d s%d %d->%d @%dx%d B%d: %s bn=%d patch=%dx%dx%d tiles=%d grid=%d stages=%d kgroup=%d bstat=%d smem=%u\n",
-                 g.kh, g.kw, g.stride, g.Cin, g.Cout, g.H, g.W, g.B, pl->dual ? "dual-M" : "generic", pl->block_n, bw, bh, bn,
-                 pl->dual ? pl->dp.total_items : p.total_tiles, pl->grid, pl->dual ? pl->dp.num_stages : p.num_stages, p.kgroup,
+                 g.kh, g.kw, g.stride, g.Cin, g.Cout, g.H, g.W, g.B, pl->pair ? "pair (2-CTA)" : (pl->dual ? "dual-M" : "generic"), pl->block_n, bw, bh, bn,
+                 pl->pair ? pl->pp.total_items : (pl->dual ? pl->dp.total_items : p.total_tiles), pl->grid,
+                 pl->pair ? pl->pp.num_stages : (pl->dual ? pl->dp.num_stages : p.num_stages), p.kgroup,
                  p.b_stationary, pl->smem_bytes);
   return pl;
 }

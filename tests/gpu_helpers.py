@@ -249,6 +249,15 @@ CONV_CASES = [
                                                            residual=True, want_out=True, want_act=True)),
     ("wide s2 512->1024 @28 B9 shortcut", dict(B=9, H=28, W=28, Cin=512, Cout=1024, k=1, stride=2, pad=0)),
     ("wide 64->256 @13x9 B3 ragged res raw", dict(B=3, H=13, W=9, Cin=64, Cout=256, k=1, stride=1, pad=0, residual=True)),
+    # CTA-pair kernel (tcgen05.mma.cta_group::2, one 256 x N tile per 2-SM cluster): N = 128 halves, an odd number of
+    # M tiles (the pair's second tile lies wholly outside the batch), one pair only, more items than clusters x 2
+    # (both accumulators of the double buffer reused), strided 3x3 taps through the pair's TMA loads
+    ("pair 1x1 512->128 @28 B20 (N=128)", dict(B=20, H=28, W=28, Cin=512, Cout=128, k=1, stride=1, pad=0, relu=1)),
+    ("pair 3x3 256->256 @14 B9 (odd M tiles)", dict(B=9, H=14, W=14, Cin=256, Cout=256, k=3, stride=1, pad=1, relu=1)),
+    ("pair 1x1 1024->256 @14 B1 (one pair)", dict(B=1, H=14, W=14, Cin=1024, Cout=256, k=1, stride=1, pad=0)),
+    ("pair 1x1 1024->256 @14 B256 (196 items)", dict(B=256, H=14, W=14, Cin=1024, Cout=256, k=1, stride=1, pad=0, relu=1)),
+    ("pair 3x3 s2 256->256 @28 B70", dict(B=70, H=28, W=28, Cin=256, Cout=256, k=3, stride=2, pad=1, relu=1)),
+    ("pair 1x1 2048->512 @7 B200 (two N tiles)", dict(B=200, H=7, W=7, Cin=2048, Cout=512, k=1, stride=1, pad=0, relu=1)),
     # large-K plain 1x1 conv with at least two waves of tiles: the wide kernel's four-stage configuration
     ("deep 512->256 @28 B50 (306 tiles)", dict(B=50, H=28, W=28, Cin=512, Cout=256, k=1, stride=1, pad=0, relu=1)),
 ]

@@ -14,11 +14,26 @@ import gpu_helpers as gh  # noqa: E402
 def test_conv2d(dtype, name, kw, monkeypatch):
     if name.startswith("wide"):
         monkeypatch.setenv("B200RN_WIDE", "2")      # also the residual-free shapes go through conv_wide_kernel
+    if name.startswith("pair"):
+        monkeypatch.setenv("B200RN_PAIR", "2")      # also Cout = 128 layers go through conv_pair_kernel (N = 128 tile)
     r = gh.conv_case(dtype, **kw)
     assert r["rc"] == 0, r["msg"]
     for key in ("out", "act"):
         if key in r:
             assert r[key]["viol"] == 0, (name, key, r[key])
+
+
+SINGLE_SM_CASES = [c for c in gh.CONV_CASES if "dual-M" in c[0] or c[0].startswith("pair")]
+
+
+@pytest.mark.parametrize("dtype", [1, 2], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("name,kw", SINGLE_SM_CASES, ids=[c[0] for c in SINGLE_SM_CASES])
+def test_conv2d_large_k_without_cta_pairs(dtype, name, kw, monkeypatch):
+    """B200RN_PAIR=0: the same large-K shapes on the single-SM kernels (dual-M / deep / generic) the pair kernel replaced."""
+    monkeypatch.setenv("B200RN_PAIR", "0")
+    r = gh.conv_case(dtype, **kw)
+    assert r["rc"] == 0, r["msg"]
+    assert r["out"]["viol"] == 0, (name, r["out"])
 
 
 @pytest.mark.parametrize("dtype", [1, 2], ids=["bf16", "fp16"])

@@ -8,9 +8,9 @@ src/inference_engine.cpp:134-209).
 Bars (BASELINE.json north_star), all constants fixed here in advance:
   exact mode   max-abs logit error <= 1e-3 and top-1 equal on all 258 samples.
   fp16 / bf16  max-abs <= ABS_BOUND and top-1 equal on every sample whose fp64-oracle top-1/top-2 margin exceeds
-               MARGIN[mode].  MARGIN is 6*sqrt(2) x the mode's RMS logit error measured in round 1 (0.016 fp16,
-               0.125 bf16 on this fixture, logit std 2.9): the distance at which two logits with independent errors
-               of that size cannot change order.  It does NOT move with the error measured in the run.  The fp32 and
+               MARGIN[mode].  MARGIN is about ten times the mode's RMS logit error as measured once on B200 on this
+               set (0.0146 fp16, 0.112 bf16; logit std 1.63): a distance at which two logits with independent errors
+               of that size do not change order.  It does NOT move with the error measured in the run.  The fp32 and
                fp64 oracles agree on all 258 top-1 classes (tests/golden/resnet50_parity258_seed0.npz), so samples
                below the margin are near-ties for a 16-bit implementation only; they are counted and printed
                ("plain" agreement), and the plain agreement has its own floor.
@@ -32,7 +32,7 @@ pkg = b200rn_loader.load_package()
 
 ABS_BOUND = {"exact": 1e-3, "fp16": 0.2, "bf16": 1.5}
 MARGIN = {"exact": 0.0, "fp16": 0.15, "bf16": 1.0}
-PLAIN_FLOOR = {"exact": 258, "fp16": 245, "bf16": 200}     # of 258
+PLAIN_FLOOR = {"exact": 258, "fp16": 252, "bf16": 215}     # of 258 (measured on B200: 258, 256, 225)
 
 
 @pytest.fixture(scope="module")
