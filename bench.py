@@ -243,6 +243,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--mode", default="fp16", choices=["fp16", "bf16", "exact"])
+    ap.add_argument("--exact-simt", action="store_true", help="exact mode on the fp32 CUDA-core conv kernel (B200RN_EXACT_SIMT=1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sustain-s", type=float, default=5.0, help="length of the sustained leg in seconds (0 = skip)")
     ap.add_argument("--layers-out", default="", help="write the per-layer roofline table (JSON) here")
@@ -255,6 +256,8 @@ def main():
     if args.dry_run_dist:
         return dry_run_dist(args)
 
+    if args.exact_simt:
+        os.environ["B200RN_EXACT_SIMT"] = "1"
     import numpy as np
     import torch
     import b200rn_loader
@@ -431,6 +434,11 @@ def main():
         # frac divides by the SUSTAINED bf16 peak (seconds-long cuBLAS loop at the power cap, ~1.34 GHz); the timed
         # region here is a sub-second burst at up to 1.965 GHz, for which the burst peak is the like-for-like
         # denominator: frac_burst.  frac_sustained_leg divides the >= 5 s leg's whole-step rate by the sustained peak.
+        if args.mode == "exact":
+            # exact mode multiplies in TF32 (half the bf16 rate; no separate measured peak on this pool) and issues three
+            # TF32 products per algorithmic product, so frac <= 1/3 by construction
+            pk = dict(pk, tflops=pk["tflops"] / 2, tflops_burst=pk["tflops_burst"] / 2,
+                      source=pk["source"] + " / 2 for kind::tf32; 3 TF32 MMAs per algorithmic product")
         roof = {"bound": "tensor", "kernel": "tcgen05 conv kernels (%d launches/step: conv_pair, conv_umma, conv_wide, conv_tail, conv_dualm, conv3x3_halo, stem7x7)" % len(conv),
                 "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
                 "peak_kind": "bf16_tflops_sustained", "peak_burst": pk["tflops_burst"], "frac_burst": achieved / pk["tflops_burst"],
@@ -481,7 +489,7 @@ def main():
             "config": {"workload": "offline batched ResNet-50 v2 forward (BASELINE configs[3] at batch %d; batch 32 = configs[1] "
                                    "cap reported under batch32), synthetic N(0,1) 3x224x224 fp32 NCHW inputs, random-init "
                                    "weights of the resnet50-v2-7 topology" % B,
-                       "batch": B, "mode": args.mode, "replicas": world, "parallelism": "replica per GPU, no collective", "numa_node_rank0": numa,
+                       "batch": B, "mode": args.mode + ("-simt" if args.exact_simt else ""), "replicas": world, "parallelism": "replica per GPU, no collective", "numa_node_rank0": numa,
                        "l2": "inputs larger than L2: %d rotating device batches of %.0f MB" % (n_rot, in_bytes / 1e6),
                        "flop_per_image": FLOP_PER_IMAGE},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": out_bytes,

@@ -83,6 +83,7 @@ _sig("b200rn_lru_size", C.c_size_t, [_vp])
 _sig("b200rn_lru_hits", C.c_size_t, [_vp])
 _sig("b200rn_lru_misses", C.c_size_t, [_vp])
 _sig("b200rn_batch_selftest", None, [C.c_int] * 5 + [C.POINTER(C.c_longlong), C.POINTER(C.c_double)])
+_sig("b200rn_batch_selftest2", None, [C.c_int] * 7 + [C.POINTER(C.c_longlong), C.POINTER(C.c_double)])
 
 
 class B200RNError(RuntimeError):

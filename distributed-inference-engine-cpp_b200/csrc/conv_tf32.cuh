@@ -6,17 +6,21 @@
 //     a * w  ~=  a_hi * w_hi  +  a_hi * w_lo  +  a_lo * w_hi          (the dropped a_lo * w_lo is ~2^-22 relative)
 // The weights are split once on the host ([Cout][K] hi and lo arrays).  The activation tile arrives by TMA as raw fp32
 // and four transform warps split it in shared memory (hi in place, lo into a second buffer of the same swizzled layout)
-// before the MMA thread sees the stage.  Per K step of 8 channels two instructions are issued:
-//     D[:, 0 .. 2N)   += A_hi * [W_hi ; W_lo]^T     one M128 x 2N x K8 MMA over the hi and lo weight tiles, which sit back
-//                                                   to back in shared memory: columns [0, N) collect hi*hi, [N, 2N) hi*lo
-//     D[:, N .. 2N)   += A_lo * W_hi^T              M128 x N x K8
-// so the small terms are summed among themselves and added to the large one only once, in the epilogue
-// (v = D[c] + D[N + c] + bias).  An accumulator is 2N columns; two of them fill tensor memory at N = 128.
+// before the MMA thread sees the stage.  Per K step of 8 channels three M128 x N x K8 instructions are issued:
+//     MAIN += A_hi * W_hi^T          LO += A_hi * W_lo^T          LO += A_lo * W_hi^T
+// Two-level accumulation.  The tensor core's fp32 accumulate truncates instead of rounding, a one-sided error of about
+// half an ulp per instruction that grows linearly with the length of the chain: measured 1.5e-5 relative at K = 2304
+// (288 K steps) with everything accumulated in tensor memory, 1.4e-3 max-abs on the logits -- over the 1e-3 bar.  So
+// MAIN only ever accumulates a chunk of kT32ChunkBlocks K blocks (16 K steps); it alternates between two tensor-memory
+// buffers and the epilogue warps add every finished chunk into fp32 REGISTERS (N/2 per thread) with properly rounded
+// adds while the next chunk is being multiplied.  LO is 2^-11 of MAIN, its truncation error is negligible, and it stays
+// in tensor memory for the whole K (double-buffered across tiles).  v = registers + LO + bias.
 // Epilogue (8 warps): bias, ReLU, residual (read straight from global memory, 128 contiguous bytes per thread), raw and/or
 // BN-ReLU'd output staged in swizzled shared memory and written by TMA stores, 32 channels (128 bytes) per chunk.
 // K is ordered (ky, kx, cin) in blocks of 32 channels; the operand box is {32 ch, bw, bh, bn} fp32 with the conv's
 // stride as element stride and TMA zero fill as padding, exactly like the 16-bit kernels.
 constexpr int kT32XfWarps = 4;
+constexpr int kT32ChunkBlocks = 4;          // K blocks (of 32 channels) per MAIN chunk
 constexpr int kT32Threads = 64 + kT32XfWarps * 32 + kEpiThreads;     // TMA, MMA, 4 transform warps, 8 epilogue warps
 
 struct Tf32Params {
@@ -68,7 +72,8 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   constexpr uint32_t A_BYTES = kTileM * 128;          // 128 rows x 32 fp32
   constexpr uint32_t B_BYTES = BLOCK_N * 128;         // one of the two weight tiles
   constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;   // A_hi | A_lo | W_hi | W_lo
-  constexpr uint32_t ACC_COLS = 2 * BLOCK_N;
+  // tensor memory: MAIN chunk buffers 0/1 at columns [0, N) and [N, 2N); LO accumulators 0/1 at [2N, 3N) and [3N, 4N)
+  constexpr uint32_t TMEM_COLS = 4 * BLOCK_N;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -80,9 +85,11 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   uint64_t* full_bar = bars;                  // [S]  TMA -> transform warps
   uint64_t* xf_bar = full_bar + S;            // [S]  transform warps -> MMA (4 warp arrivals)
   uint64_t* empty_bar = xf_bar + S;           // [S]  MMA -> TMA
-  uint64_t* tmem_full = empty_bar + S;        // [2]
-  uint64_t* tmem_empty = tmem_full + 2;       // [2]  (8 warp arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* main_full = empty_bar + S;        // [2]  MMA -> epilogue: a MAIN chunk is complete
+  uint64_t* main_empty = main_full + 2;       // [2]  epilogue -> MMA (8 warp arrivals): chunk added into registers
+  uint64_t* lo_full = main_empty + 2;         // [2]  MMA -> epilogue: a tile's LO accumulator is complete
+  uint64_t* lo_empty = lo_full + 2;           // [2]  epilogue -> MMA (8 warp arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(lo_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int my_tiles = (int(blockIdx.x) < p.total_tiles) ? (p.total_tiles - 1 - int(blockIdx.x)) / int(gridDim.x) + 1 : 0;
@@ -96,10 +103,13 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       mbar_init(smem_u32(&xf_bar[i]), kT32XfWarps);
       mbar_init(smem_u32(&empty_bar[i]), 1);
     }
-    for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&tmem_full[i]), 1); mbar_init(smem_u32(&tmem_empty[i]), kEpiWarps); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&main_full[i]), 1); mbar_init(smem_u32(&main_empty[i]), kEpiWarps);
+      mbar_init(smem_u32(&lo_full[i]), 1); mbar_init(smem_u32(&lo_empty[i]), kEpiWarps);
+    }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 2 * ACC_COLS >= 512 ? 512 : (2 * ACC_COLS));
+  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -140,31 +150,42 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     }
   } else if (warp == 1) {
     // ===== MMA issuer (one thread) =====
-    constexpr uint32_t idesc_wide = make_idesc_tf32<2 * BLOCK_N>();
-    constexpr uint32_t idesc_one = make_idesc_tf32<BLOCK_N>();
+    constexpr uint32_t idesc = make_idesc_tf32<BLOCK_N>();
     constexpr uint32_t desc_hi = smem_desc_hi<128>();
     if (elect_one()) {
       const uint32_t pipe_lo = smem_desc_lo(smem_u32(pipe));
       int stage = 0;
       uint32_t phase = 0;
+      uint32_t chunk = 0;                   // running MAIN chunk counter over all of this CTA's tiles
       for (int i = 0; i < my_tiles; ++i) {
-        const int buf = i & 1;
-        mbar_wait(smem_u32(&tmem_empty[buf]), ((uint32_t(i) >> 1) & 1) ^ 1);
+        const int lbuf = i & 1;
+        mbar_wait(smem_u32(&lo_empty[lbuf]), ((uint32_t(i) >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t tmem_d = tmem_base + uint32_t(buf) * ACC_COLS;
+        const uint32_t tmem_lo = tmem_base + uint32_t(2 + lbuf) * BLOCK_N;
         for (int it = 0; it < p.num_k_iters; ++it) {
+          const int in_chunk = it % kT32ChunkBlocks;
+          const uint32_t mbuf = chunk & 1;
+          if (in_chunk == 0) {
+            mbar_wait(smem_u32(&main_empty[mbuf]), ((chunk >> 1) & 1) ^ 1);   // the epilogue has taken this buffer's last chunk
+            tc_fence_after();
+          }
+          const uint32_t tmem_main = tmem_base + mbuf * BLOCK_N;
           mbar_wait(smem_u32(&xf_bar[stage]), phase);
           tc_fence_after();
           const uint32_t ahi = pipe_lo + uint32_t(stage) * (STAGE_BYTES >> 4);
           const uint32_t alo = ahi + (A_BYTES >> 4);
           const uint32_t bhi = ahi + 2 * (A_BYTES >> 4);
+          const uint32_t blo = bhi + (B_BYTES >> 4);
 #pragma unroll
           for (int k = 0; k < 4; ++k) {       // K = 8 fp32 = 32 bytes per instruction
-            umma_tf32_lo(tmem_d, ahi + 2 * k, bhi + 2 * k, desc_hi, idesc_wide, (it | k) != 0 ? 1u : 0u);
-            umma_tf32_lo(tmem_d + BLOCK_N, alo + 2 * k, bhi + 2 * k, desc_hi, idesc_one, 1u);
+            umma_tf32_lo(tmem_main, ahi + 2 * k, bhi + 2 * k, desc_hi, idesc, (in_chunk | k) != 0 ? 1u : 0u);
+            umma_tf32_lo(tmem_lo, ahi + 2 * k, blo + 2 * k, desc_hi, idesc, (it | k) != 0 ? 1u : 0u);
+            umma_tf32_lo(tmem_lo, alo + 2 * k, bhi + 2 * k, desc_hi, idesc, 1u);
           }
           umma_commit(smem_u32(&empty_bar[stage]));
-          if (it == p.num_k_iters - 1) umma_commit(smem_u32(&tmem_full[buf]));
+          const bool last = it == p.num_k_iters - 1;
+          if (in_chunk == kT32ChunkBlocks - 1 || last) { umma_commit(smem_u32(&main_full[mbuf])); ++chunk; }
+          if (last) umma_commit(smem_u32(&lo_full[lbuf]));
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
       }
@@ -205,6 +226,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     const uint32_t out_row = smem_u32(outbuf) + uint32_t(row) * 128u;
     const uint32_t act_row = smem_u32(actbuf) + uint32_t(row) * 128u;
     int cc = 0;
+    uint32_t mchunk = 0;                        // running MAIN chunk counter (same sequence as the MMA thread's)
     for (int i = 0; i < my_tiles; ++i) {
       int w0, h0, n0, col0;
       tile_coord(i, w0, h0, n0, col0);
@@ -214,14 +236,34 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       const int ox = w0 + px, oy = h0 + py, on = n0 + pn;
       const bool in_range = row < int(p.rows) && ox < p.Wo && oy < p.Ho && on < p.B;
       const float* res_px = p.residual + ((size_t(on) * p.Ho + oy) * p.Wo + ox) * size_t(p.cout);
-      mbar_wait(smem_u32(&tmem_full[buf]), (uint32_t(i) >> 1) & 1);
+      // ---- level 2 of the accumulation: every finished MAIN chunk is added into registers ----
+      float sum[kChunks * 16];
+#pragma unroll
+      for (int k = 0; k < kChunks * 16; ++k) sum[k] = 0.f;
+      const int n_chunks = (p.num_k_iters + kT32ChunkBlocks - 1) / kT32ChunkBlocks;
+      for (int kc = 0; kc < n_chunks; ++kc, ++mchunk) {
+        const uint32_t mbuf = mchunk & 1;
+        mbar_wait(smem_u32(&main_full[mbuf]), (mchunk >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+          uint32_t d[16];
+          tmem_ld_32x32b_x16(lane_addr + mbuf * BLOCK_N + uint32_t(c * 32 + g * 16), d);
+          tmem_ld_wait();
+#pragma unroll
+          for (int k = 0; k < 16; ++k) sum[c * 16 + k] += __uint_as_float(d[k]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&main_empty[mbuf]));
+      }
+      mbar_wait(smem_u32(&lo_full[buf]), (uint32_t(i) >> 1) & 1);
       tc_fence_after();
-#pragma unroll 1
+#pragma unroll
       for (int c = 0; c < kChunks; ++c, ++cc) {
         const int ch0 = c * 32 + g * 16;            // first of this thread's 16 channels within the N tile
-        uint32_t d0[16], d1[16];
-        tmem_ld_32x32b_x16(lane_addr + uint32_t(buf) * ACC_COLS + uint32_t(ch0), d0);
-        tmem_ld_32x32b_x16(lane_addr + uint32_t(buf) * ACC_COLS + uint32_t(BLOCK_N + ch0), d1);
+        uint32_t d1[16];
+        tmem_ld_32x32b_x16(lane_addr + uint32_t(2 + buf) * BLOCK_N + uint32_t(ch0), d1);
         float4 bv[4], rv[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) bv[k] = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + ch0) + k);
@@ -234,17 +276,17 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         if (c == kChunks - 1) {             // accumulator fully read: hand it back to the MMA thread
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(smem_u32(&tmem_empty[buf]));
+          if (lane == 0) mbar_arrive(smem_u32(&lo_empty[buf]));
         }
         if (store_thread && cc > 0) tma_store_wait_read();   // the previous chunk's stores have read both staging buffers
         asm volatile("bar.sync 1, 256;" ::: "memory");
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           float v[4];
-          v[0] = __uint_as_float(d0[4 * k + 0]) + __uint_as_float(d1[4 * k + 0]) + bv[k].x;
-          v[1] = __uint_as_float(d0[4 * k + 1]) + __uint_as_float(d1[4 * k + 1]) + bv[k].y;
-          v[2] = __uint_as_float(d0[4 * k + 2]) + __uint_as_float(d1[4 * k + 2]) + bv[k].z;
-          v[3] = __uint_as_float(d0[4 * k + 3]) + __uint_as_float(d1[4 * k + 3]) + bv[k].w;
+          v[0] = sum[c * 16 + 4 * k + 0] + __uint_as_float(d1[4 * k + 0]) + bv[k].x;
+          v[1] = sum[c * 16 + 4 * k + 1] + __uint_as_float(d1[4 * k + 1]) + bv[k].y;
+          v[2] = sum[c * 16 + 4 * k + 2] + __uint_as_float(d1[4 * k + 2]) + bv[k].z;
+          v[3] = sum[c * 16 + 4 * k + 3] + __uint_as_float(d1[4 * k + 3]) + bv[k].w;
           if (p.relu) { v[0] = fmaxf(v[0], 0.f); v[1] = fmaxf(v[1], 0.f); v[2] = fmaxf(v[2], 0.f); v[3] = fmaxf(v[3], 0.f); }
           if (p.has_res) { v[0] += rv[k].x; v[1] += rv[k].y; v[2] += rv[k].z; v[3] += rv[k].w; }
           const uint32_t slot16 = uint32_t(((g * 4 + k) ^ sw) << 4);      // SWIZZLE_128B: 16-byte slot XOR (row mod 8)
@@ -272,5 +314,5 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 2 * ACC_COLS >= 512 ? 512 : (2 * ACC_COLS));
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
 }

@@ -1343,6 +1343,7 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #include "conv_tail.cuh"
 #include "conv_wide.cuh"
 #include "conv_pair.cuh"
+#include "conv_tf32.cuh"
 
 // ---- host side --------------------------------------------------------------------------------
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -2310,6 +2311,138 @@ void umma_conv_plan_destroy(UmmaConvPlan* p) {
     cudaFree(p->hp.trace);
   }
   delete p;
+}
+
+
+// ---- exact mode on the tensor cores: 3 x TF32 (conv_tf32.cuh) --------------------------------------------------
+struct Tf32ConvPlan {
+  ConvGeom g;
+  int block_n;
+  Tf32Params p;
+  CUtensorMap tmA, tmWhi, tmWlo, tmOut, tmAct;
+  uint32_t smem_bytes;
+  int grid;
+};
+
+bool tf32_conv_supported(const ConvGeom& g) {
+  return g.Cin % 32 == 0 && g.Cout % 64 == 0 && g.kh == g.kw && (g.stride == 1 || g.stride == 2);
+}
+
+void tf32_split_weights(const float* w, size_t n, float* hi, float* lo) {
+  for (size_t i = 0; i < n; ++i) {
+    uint32_t u;
+    std::memcpy(&u, &w[i], 4);
+    u &= 0xFFFFE000u;
+    float h;
+    std::memcpy(&h, &u, 4);
+    float l = w[i] - h;               // exact: the 13 bits that were cut
+    std::memcpy(&u, &l, 4);
+    u &= 0xFFFFE000u;
+    std::memcpy(&l, &u, 4);
+    hi[i] = h; lo[i] = l;
+  }
+}
+
+static bool encode_f32(CUtensorMap* m, int rank, const void* base, const uint64_t* dims, const uint64_t* strides_bytes,
+                       const uint32_t* box, const uint32_t* estr, std::string& err) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) { err = "cuTensorMapEncodeTiled is not available from the driver"; return false; }
+  cuuint64_t d[5]; cuuint64_t st[4]; cuuint32_t b[5], e[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = estr[i]; }
+  for (int i = 0; i + 1 < rank; ++i) st[i] = strides_bytes[i];
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, cuuint32_t(rank), const_cast<void*>(base), d, st, b, e,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[200];
+    std::snprintf(buf, sizeof buf, "cuTensorMapEncodeTiled (fp32) failed (CUresult %d) rank=%d box=[%u,%u,%u,%u]", int(r), rank, box[0], box[1],
+                  rank > 2 ? box[2] : 0, rank > 3 ? box[3] : 0);
+    err = buf;
+    return false;
+  }
+  return true;
+}
+
+// fp32 NHWC activation [B,H,W,C] as a 4-D map (C, W, H, N) with a {32, bw*es, bh*es, bn} box
+static bool encode_act_f32(CUtensorMap* m, const void* base, int B, int H, int W, int C, int bw, int bh, int bn, int es, std::string& err) {
+  uint64_t dims[4] = {uint64_t(C), uint64_t(W), uint64_t(H), uint64_t(B)};
+  uint64_t str[3] = {uint64_t(C) * 4, uint64_t(W) * C * 4, uint64_t(H) * W * C * 4};
+  uint32_t box[4] = {32, uint32_t(bw * es), uint32_t(bh * es), uint32_t(bn)};
+  uint32_t estr[4] = {1, uint32_t(es), uint32_t(es), 1};
+  return encode_f32(m, 4, base, dims, str, box, estr, err);
+}
+
+Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g, const float* in, const float* w_hi, const float* w_lo, const Epilogue& e,
+                                    char* err, size_t errcap) {
+  auto failmsg = [&](const std::string& m) -> Tf32ConvPlan* {
+    if (err && errcap) std::snprintf(err, errcap, "%s", m.c_str());
+    return nullptr;
+  };
+  if (!tf32_conv_supported(g)) return failmsg("3xTF32 conv needs Cin % 32 == 0, Cout % 64 == 0, a square filter and stride 1 or 2");
+  if (e.pre_scale || e.tail_out || e.in_b || e.out_f32 || e.pool_fused) return failmsg("3xTF32 conv has no prologue / tail / second input / fp32-row / pool form");
+  if (!e.out && !e.out_act) return failmsg("conv with no output");
+  auto pl = new Tf32ConvPlan();
+  pl->g = g;
+  Tf32Params& p = pl->p;
+  std::memset(&p, 0, sizeof p);
+  pl->block_n = (g.Cout % 128 == 0) ? 128 : 64;
+  int bw = 1, bh = 1, bn = 1;
+  choose_patch(g.B, g.Ho, g.Wo, bw, bh, bn);
+  p.bw = bw; p.bh = bh; p.bn = bn;
+  p.tiles_w = (g.Wo + bw - 1) / bw; p.tiles_h = (g.Ho + bh - 1) / bh;
+  p.n_tiles = g.Cout / pl->block_n;
+  p.total_tiles = p.tiles_w * p.tiles_h * ((g.B + bn - 1) / bn) * p.n_tiles;
+  p.cblks = g.Cin / 32; p.kw = g.kw; p.stride = g.stride; p.pad = g.pad;
+  p.num_k_iters = g.kh * g.kw * p.cblks;
+  p.rows = uint32_t(bw * bh * bn); p.a_bytes = p.rows * 128u;
+  p.has_res = e.residual != nullptr; p.has_out = e.out != nullptr; p.has_act = e.out_act != nullptr;
+  p.relu = e.relu; p.act_relu = e.act_relu;
+  p.cout = g.Cout; p.Ho = g.Ho; p.Wo = g.Wo; p.B = g.B;
+  p.bias = e.bias; p.act_scale = e.act_scale; p.act_shift = e.act_shift;
+  p.residual = static_cast<const float*>(e.residual);
+  if (p.has_act && (!e.act_scale || !e.act_shift)) { delete pl; return failmsg("activated output needs scale and shift"); }
+  const uint32_t stage_bytes = 2u * kTileM * 128 + 2u * uint32_t(pl->block_n) * 128;
+  const uint32_t fixed = 1024u + 2 * kChunkBytes + 8u * (3 * 8 + 4) + 64;
+  p.num_stages = std::max(2, std::min(8, int((227u * 1024 - fixed) / stage_bytes)));
+  pl->smem_bytes = fixed + uint32_t(p.num_stages) * stage_bytes;
+  pl->grid = std::min(p.total_tiles, sm_count());
+  std::string msg;
+  bool ok = encode_act_f32(&pl->tmA, in, g.B, g.H, g.W, g.Cin, bw, bh, bn, g.stride, msg);
+  const uint64_t K = uint64_t(g.kh) * g.kw * g.Cin;
+  uint64_t wd[2] = {K, uint64_t(g.Cout)};
+  uint64_t ws[1] = {K * 4};
+  uint32_t wb[2] = {32, uint32_t(pl->block_n)};
+  uint32_t we[2] = {1, 1};
+  if (ok) ok = encode_f32(&pl->tmWhi, 2, w_hi, wd, ws, wb, we, msg);
+  if (ok) ok = encode_f32(&pl->tmWlo, 2, w_lo, wd, ws, wb, we, msg);
+  const void* any_out = e.out ? e.out : e.out_act;
+  if (ok) ok = encode_act_f32(&pl->tmOut, e.out ? e.out : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
+  if (ok) ok = encode_act_f32(&pl->tmAct, e.out_act ? e.out_act : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
+  if (!ok) { delete pl; return failmsg(msg); }
+  if (std::getenv("B200RN_VERBOSE"))
+    std::fprintf(stderr, "[b200rn] conv %dx%d s%d %d->%d @%dx%d B%d: 3xTF32 bn=%d patch=%dx%dx%d tiles=%d grid=%d stages=%d smem=%u\n", g.kh, g.kw,
+                 g.stride, g.Cin, g.Cout, g.H, g.W, g.B, pl->block_n, bw, bh, bn, p.total_tiles, pl->grid, p.num_stages, pl->smem_bytes);
+  return pl;
+}
+
+void tf32_conv_plan_destroy(Tf32ConvPlan* p) { delete p; }
+
+template <int BLOCK_N>
+static cudaError_t launch_tf32_inst(const Tf32ConvPlan* pl, cudaStream_t s) {
+  auto kern = conv_tf32x3_kernel<BLOCK_N>;
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    configured_device = dev;
+  }
+  return launch_pdl(kern, pl->grid, kT32Threads, pl->smem_bytes, s, pl->tmA, pl->tmWhi, pl->tmWlo, pl->tmOut, pl->tmAct, pl->p);
+}
+
+cudaError_t launch_conv_tf32(const Tf32ConvPlan* pl, cudaStream_t s) {
+  return pl->block_n == 128 ? launch_tf32_inst<128>(pl, s) : launch_tf32_inst<64>(pl, s);
 }
 
 cudaError_t umma_take_timeout_flag(unsigned int* flag) {

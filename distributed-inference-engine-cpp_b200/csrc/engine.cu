@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -68,6 +69,13 @@ bool dual_input_enabled() {
   return !(v && v[0] == '0');
 }
 
+// Exact mode: convolutions on the tensor cores as 3 x TF32 split products (conv_tf32.cuh) unless B200RN_EXACT_SIMT=1,
+// which keeps the fp32 CUDA-core kernel (the round-1 exact path; bench.py --exact-simt times it beside the new one).
+bool exact_tf32_enabled() {
+  const char* v = std::getenv("B200RN_EXACT_SIMT");
+  return !(v && v[0] == '1');
+}
+
 // FC on the tensor cores in the 16-bit modes (B200RN_FC_UMMA=0: the fp32 CUDA-core kernel, as in exact mode).
 bool fc_umma_enabled() {
   const char* v = std::getenv("B200RN_FC_UMMA");
@@ -103,6 +111,9 @@ struct DevLayer {
   float* splitk = nullptr;              // Gemm only: split-K partial sums + tile counters
   size_t splitk_bytes = 0;
   std::map<int, UmmaConvPlan*> plans;   // per batch size
+  bool tf32 = false;                    // exact mode, conv on the tensor cores: w = [Cout][K] hi parts, w_lo = lo parts
+  float* w_lo = nullptr;
+  std::map<int, Tf32ConvPlan*> tf32_plans;
   double weight_bytes = 0;
 };
 
@@ -139,7 +150,9 @@ struct b200rn {
   int stem_tensor = -1;
   cudaStream_t s_h2d = nullptr, s_compute = nullptr, s_d2h = nullptr;
   Slot slot[2];
-  mutable std::mutex mu;
+  mutable std::mutex mu;          // host-side state of the handle (plans, graphs, stream enqueue order)
+  std::mutex slot_mu[2];          // ownership of a transfer slot for the length of one b200rn_infer / infer_packed call
+  std::atomic<unsigned> slot_ticket{0};
   mutable std::string err;
   unsigned int* d_timeout_flag = nullptr;
 
@@ -149,6 +162,8 @@ struct b200rn {
       cudaFree(L.bias); cudaFree(L.act_scale); cudaFree(L.act_shift); cudaFree(L.w); cudaFree(L.splitk);
       cudaFree(L.pre_scale); cudaFree(L.pre_shift); cudaFree(L.tail_w); cudaFree(L.tail_bias); cudaFree(L.fc_in16);
       for (auto& kv : L.plans) umma_conv_plan_destroy(kv.second);
+      for (auto& kv : L.tf32_plans) tf32_conv_plan_destroy(kv.second);
+      cudaFree(L.w_lo);
     }
     for (auto& kv : graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
     cudaFree(arena);
@@ -289,6 +304,16 @@ struct b200rn {
           D.fc_cout_pad = Npad;
           CK(cudaMalloc(&D.fc_in16, size_t(max_batch) * L.Cin * 2));
           dl[size_t(plan.tensors[size_t(L.in)].def_layer)].gap_out16 = D.fc_in16;
+        } else if (L.kind == LayerKind::Conv && dt == DType::F32 && exact_tf32_enabled() && L.in_b < 0 &&
+                   L.pre_scale.empty() && L.tail_out < 0 && !L.fused_pool &&
+                   tf32_conv_supported(ConvGeom{1, 1, 1, L.Cin, 1, 1, L.Cout, L.kh, L.kw, L.stride, L.pad})) {
+          // exact mode on the tensor cores: [Cout][K] fp32 weights split into TF32 hi and lo parts
+          std::vector<float> hi(L.weight.size()), lo(L.weight.size());
+          tf32_split_weights(L.weight.data(), L.weight.size(), hi.data(), lo.data());
+          D.w = upload(hi);
+          D.w_lo = upload(lo);
+          D.tf32 = true;
+          D.weight_bytes = double(hi.size()) * 8;
         } else {
           // fp32 CUDA-core path wants W^T: [K][Cout]
           const int K = L.kind == LayerKind::Gemm ? L.Cin : L.kh * L.kw * L.Cin;
@@ -378,6 +403,14 @@ struct b200rn {
             if (!up) { D.plans.erase(B); throw CudaFail{fmt("layer '%s': %s", L.name.c_str(), msg)}; }
           }
           CK(launch_conv_umma(up, s));
+        } else if (D.tf32) {
+          Tf32ConvPlan*& tp = D.tf32_plans[B];
+          if (!tp) {
+            char msg[512] = {0};
+            tp = tf32_conv_plan_create(g, static_cast<const float*>(tptr(L.in)), static_cast<const float*>(D.w), D.w_lo, e, msg, sizeof msg);
+            if (!tp) { D.tf32_plans.erase(B); throw CudaFail{fmt("layer '%s': %s", L.name.c_str(), msg)}; }
+          }
+          CK(launch_conv_tf32(tp, s));
         } else {
           CK(launch_conv_simt_f32(static_cast<const float*>(tptr(L.in)), static_cast<const float*>(D.w), g, e, s));
         }
@@ -504,7 +537,7 @@ struct b200rn {
   }
 
   void check_kernel_health() {
-    if (dt == DType::F32) return;
+    if (dt == DType::F32 && !exact_tf32_enabled()) return;
     unsigned int flag = 0;
     CK(umma_take_timeout_flag(&flag));
     if (flag) throw CudaFail{"a tensor-core conv kernel gave up waiting on a TMA/MMA barrier; results are invalid"};
@@ -518,22 +551,38 @@ struct b200rn {
     check_kernel_health();
   }
 
+  // After a failed submit / wait nothing may stay in flight into the caller's buffers and no slot may stay "busy":
+  // wait for whatever was queued and mark both slots idle (errors here are ignored: one is already being reported).
+  void drain_slots() {
+    for (auto& s : slot)
+      if (s.busy) {
+        cudaEventSynchronize(s.done);
+        s.busy = false;
+      }
+    cudaGetLastError();
+  }
+
   // whole batch in slices of max_batch, alternating slots so transfers overlap compute
   void run_packed(const float* nchw, size_t batch, float* out) {
     const size_t ie = size_t(plan.in_elems_per_sample), oe = size_t(plan.out_elems_per_sample);
     size_t done = 0;
     int si = 0;
     bool pending[2] = {false, false};
-    while (done < batch) {
-      size_t n = std::min(batch - done, size_t(max_batch));
-      if (pending[si]) { wait(si); pending[si] = false; }
-      submit(si, nchw + done * ie, n, out + done * oe);
-      pending[si] = true;
-      done += n;
-      si ^= 1;
+    try {
+      while (done < batch) {
+        size_t n = std::min(batch - done, size_t(max_batch));
+        if (pending[si]) { pending[si] = false; wait(si); }
+        submit(si, nchw + done * ie, n, out + done * oe);
+        pending[si] = true;
+        done += n;
+        si ^= 1;
+      }
+      for (int k = 0; k < 2; ++k)
+        if (pending[k]) { pending[k] = false; wait(k); }
+    } catch (...) {
+      drain_slots();
+      throw;
     }
-    for (int k = 0; k < 2; ++k)
-      if (pending[k]) wait(k);
   }
 };
 
@@ -593,49 +642,102 @@ int64_t b200rn_output_elems(const b200rn_t* h) { return h ? h->plan.out_elems_pe
 
 int b200rn_infer_packed(b200rn_t* h, const float* nchw, size_t batch, float* out) {
   if (!h) { g_error = "null handle"; return B200RN_ERR_ARG; }
-  std::lock_guard<std::mutex> lk(h->mu);
   if (batch == 0) return B200RN_OK;
+  std::lock_guard<std::mutex> s0(h->slot_mu[0]);
+  std::lock_guard<std::mutex> s1(h->slot_mu[1]);
+  std::lock_guard<std::mutex> lk(h->mu);
   if (!nchw || !out) { h->err = "b200rn_infer_packed: null buffer"; return B200RN_ERR_ARG; }
   return guarded(h, [&] { CK(cudaSetDevice(h->device)); h->run_packed(nchw, batch, out); });
 }
 
 int b200rn_infer(b200rn_t* h, const float* const* samples, const size_t* sample_len, size_t batch, float* out) {
   if (!h) { g_error = "null handle"; return B200RN_ERR_ARG; }
-  std::lock_guard<std::mutex> lk(h->mu);
   if (batch == 0) return B200RN_OK;   // reference: empty batch -> {} (src/inference_engine.cpp:137-139)
-  if (!samples || !sample_len || !out) { h->err = "b200rn_infer: null argument"; return B200RN_ERR_ARG; }
   const size_t ie = size_t(h->plan.in_elems_per_sample), oe = size_t(h->plan.out_elems_per_sample);
-  for (size_t i = 0; i < batch; ++i) {
-    if (!samples[i] && sample_len[i]) { h->err = fmt("b200rn_infer: sample %zu is null", i); return B200RN_ERR_ARG; }
-    if (sample_len[i] > ie) {
-      h->err = fmt("b200rn_infer: sample %zu has %zu values, the model input holds %zu", i, sample_len[i], ie);
-      return B200RN_ERR_ARG;
+  {
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!samples || !sample_len || !out) { h->err = "b200rn_infer: null argument"; return B200RN_ERR_ARG; }
+    for (size_t i = 0; i < batch; ++i) {
+      if (!samples[i] && sample_len[i]) { h->err = fmt("b200rn_infer: sample %zu is null", i); return B200RN_ERR_ARG; }
+      if (sample_len[i] > ie) {
+        h->err = fmt("b200rn_infer: sample %zu has %zu values, the model input holds %zu", i, sample_len[i], ie);
+        return B200RN_ERR_ARG;
+      }
     }
   }
+  // pack (zero-padded) straight into the slot's pinned staging buffer: the only host copy
+  auto pack = [&](Slot& s, size_t first, size_t n) {
+    for (size_t i = 0; i < n; ++i) {
+      float* dst = s.h_in + i * ie;
+      size_t len = sample_len[first + i];
+      if (len) std::memcpy(dst, samples[first + i], len * 4);
+      if (len < ie) std::memset(dst + len, 0, (ie - len) * 4);
+    }
+  };
+  auto ensure_staging = [&](Slot& s) {
+    if (!s.h_in) CK(cudaMallocHost(&s.h_in, size_t(h->max_batch) * ie * 4));
+  };
+  if (batch <= size_t(h->max_batch)) {
+    // One slice: the call owns ONE transfer slot, and only the enqueue holds the handle's mutex.  A second thread
+    // calling b200rn_infer meanwhile takes the other slot, so its packing, its PCIe transfers and the caller-side
+    // work around the call overlap this batch's forward (two batches in flight; the reference runs one synchronous
+    // Session::Run at a time under a mutex, src/inference_engine.cpp:136,176-183).
+    int si;
+    std::unique_lock<std::mutex> own(h->slot_mu[0], std::try_to_lock);
+    if (own.owns_lock()) si = 0;
+    else {
+      own = std::unique_lock<std::mutex>(h->slot_mu[1], std::try_to_lock);
+      if (own.owns_lock()) si = 1;
+      else {
+        si = int(h->slot_ticket.fetch_add(1) & 1u);
+        own = std::unique_lock<std::mutex>(h->slot_mu[si]);
+      }
+    }
+    Slot& s = h->slot[si];
+    int rc = guarded(h, [&] {
+      CK(cudaSetDevice(h->device));
+      { std::lock_guard<std::mutex> lk(h->mu); ensure_staging(s); }
+      pack(s, 0, batch);
+      { std::lock_guard<std::mutex> lk(h->mu); h->submit(si, s.h_in, batch, out); }
+      const cudaError_t we = cudaEventSynchronize(s.done);       // not under the handle's mutex: the other slot may enqueue
+      std::lock_guard<std::mutex> lk(h->mu);
+      s.busy = false;
+      CK(we);
+      h->check_kernel_health();
+    });
+    if (rc != B200RN_OK) {
+      std::lock_guard<std::mutex> lk(h->mu);
+      if (s.busy) { cudaEventSynchronize(s.done); s.busy = false; cudaGetLastError(); }
+    }
+    return rc;
+  }
+  // more samples than max_batch: slices alternate over both slots
+  std::lock_guard<std::mutex> s0(h->slot_mu[0]);
+  std::lock_guard<std::mutex> s1(h->slot_mu[1]);
+  std::lock_guard<std::mutex> lk(h->mu);
   return guarded(h, [&] {
     CK(cudaSetDevice(h->device));
-    // pack (zero-padded) straight into pinned staging, slice by slice, alternating slots
     size_t done = 0;
     int si = 0;
     bool pending[2] = {false, false};
-    while (done < batch) {
-      size_t n = std::min(batch - done, size_t(h->max_batch));
-      Slot& s = h->slot[si];
-      if (pending[si]) { h->wait(si); pending[si] = false; }
-      if (!s.h_in) CK(cudaMallocHost(&s.h_in, size_t(h->max_batch) * ie * 4));
-      for (size_t i = 0; i < n; ++i) {
-        float* dst = s.h_in + i * ie;
-        size_t len = sample_len[done + i];
-        if (len) std::memcpy(dst, samples[done + i], len * 4);
-        if (len < ie) std::memset(dst + len, 0, (ie - len) * 4);
+    try {
+      while (done < batch) {
+        size_t n = std::min(batch - done, size_t(h->max_batch));
+        Slot& s = h->slot[si];
+        if (pending[si]) { pending[si] = false; h->wait(si); }
+        ensure_staging(s);
+        pack(s, done, n);
+        h->submit(si, s.h_in, n, out + done * oe);
+        pending[si] = true;
+        done += n;
+        si ^= 1;
       }
-      h->submit(si, s.h_in, n, out + done * oe);
-      pending[si] = true;
-      done += n;
-      si ^= 1;
+      for (int k = 0; k < 2; ++k)
+        if (pending[k]) { pending[k] = false; h->wait(k); }
+    } catch (...) {
+      h->drain_slots();
+      throw;
     }
-    for (int k = 0; k < 2; ++k)
-      if (pending[k]) h->wait(k);
   });
 }
 
@@ -814,7 +916,27 @@ int b200rn_conv2d(int dtype, const void* d_in, int B, int H, int W, int Cin, con
     e.residual = d_residual; e.out = d_out; e.out_act = d_out_act;
     e.pre_scale = dps; e.pre_shift = dpt; e.pre_relu = pre_relu;
     void* dw = nullptr;
-    if (dt == DType::F32) {
+    if (dt == DType::F32 && exact_tf32_enabled() && !pre_scale && tf32_conv_supported(g)) {
+      // exact mode on the tensor cores (3 x TF32), as the engine runs it
+      const size_t n = size_t(Cout) * kh * kw * Cin;
+      std::vector<float> hi(n), lo(n);
+      tf32_split_weights(w, n, hi.data(), lo.data());
+      float* dhi = upload(hi);
+      float* dlo = upload(lo);
+      struct W2 { float* a; float* b; ~W2() { cudaFree(a); cudaFree(b); } } w2{dhi, dlo};
+      char msg[512] = {0};
+      Tf32ConvPlan* tp = tf32_conv_plan_create(g, static_cast<const float*>(d_in), dhi, dlo, e, msg, sizeof msg);
+      if (!tp) { cudaFree(db); cudaFree(ds); cudaFree(dsh); throw CudaFail{std::string("b200rn_conv2d: ") + msg}; }
+      cudaError_t le = launch_conv_tf32(tp, 0);
+      cudaError_t se = cudaDeviceSynchronize();
+      tf32_conv_plan_destroy(tp);
+      unsigned int flag = 0;
+      if (se == cudaSuccess) se = umma_take_timeout_flag(&flag);
+      if (le != cudaSuccess || se != cudaSuccess || flag) {
+        cudaFree(db); cudaFree(ds); cudaFree(dsh);
+        throw CudaFail{fmt("b200rn_conv2d (3xTF32): launch %s / sync %s / barrier timeout %u", cudaGetErrorString(le), cudaGetErrorString(se), flag)};
+      }
+    } else if (dt == DType::F32) {
       const int K = kh * kw * Cin;
       std::vector<float> wt(size_t(K) * Cout);
       for (int o = 0; o < Cout; ++o)

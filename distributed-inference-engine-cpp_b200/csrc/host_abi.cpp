@@ -81,4 +81,39 @@ void b200rn_batch_selftest(int max_batch, int timeout_ms, int callback_ms, int s
   *avg_batch = m.avg_batch_size;
 }
 
+void b200rn_batch_selftest2(int max_batch, int timeout_ms, int callback_ms, int submitters, int per_thread, int fill_wait,
+                            int in_flight, long long* out, double* avg_batch) {
+  std::atomic<int> running{0}, peak{0};
+  BatchProcessor<int, int> bp(size_t(max_batch), std::chrono::milliseconds(timeout_ms),
+                              [&, callback_ms](const std::vector<int>& xs) {
+                                const int now = ++running;
+                                int seen = peak.load();
+                                while (now > seen && !peak.compare_exchange_weak(seen, now)) {}
+                                std::this_thread::sleep_for(std::chrono::milliseconds(callback_ms));
+                                --running;
+                                std::vector<int> ys;
+                                ys.reserve(xs.size());
+                                for (int x : xs) ys.push_back(x + 1);
+                                return ys;
+                              });
+  bp.setFillWait(fill_wait != 0);
+  bp.setInFlight(in_flight);
+  bp.start();
+  std::atomic<long long> wrong{0};
+  std::vector<std::thread> ts;
+  for (int t = 0; t < submitters; ++t)
+    ts.emplace_back([&, t] {
+      for (int i = 0; i < per_thread; ++i) {
+        int x = t * 1000 + i;
+        if (bp.process(x) != x + 1) ++wrong;
+      }
+    });
+  for (auto& t : ts) t.join();
+  auto m = bp.getMetrics();
+  bp.stop();
+  out[0] = m.total_requests; out[1] = m.total_batches; out[2] = m.timeout_batches; out[3] = m.full_batches;
+  out[4] = wrong.load(); out[5] = peak.load();
+  *avg_batch = m.avg_batch_size;
+}
+
 }  // extern "C"

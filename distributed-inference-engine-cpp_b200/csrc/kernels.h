@@ -106,4 +106,15 @@ void umma_pack_weights(const float* w, const ConvGeom& g, DType dt, int stem_mod
 cudaError_t umma_take_timeout_flag(unsigned int* flag);
 bool umma_conv_supported(const ConvGeom& g, int stem_mode, char* why, size_t cap);
 
+
+// ---- exact mode on the tensor cores: fp32 storage, 3 x TF32 split products (conv_tf32.cuh) ------------------
+struct Tf32ConvPlan;
+bool tf32_conv_supported(const ConvGeom& g);
+// w: [Cout][kh][kw][Cin] fp32 -> hi (low 13 mantissa bits cleared) and lo (w - hi, cut the same way)
+void tf32_split_weights(const float* w, size_t n, float* hi, float* lo);
+Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g, const float* in, const float* w_hi, const float* w_lo, const Epilogue& e,
+                                    char* err, size_t errcap);
+void tf32_conv_plan_destroy(Tf32ConvPlan*);
+cudaError_t launch_conv_tf32(const Tf32ConvPlan* p, cudaStream_t s);
+
 }  // namespace rn

@@ -16,6 +16,9 @@
 // Optional policy (off by default, because it changes the /health counters): setFillWait(true)
 // makes the consumer wait up to `timeout` for the batch to fill once the first request arrived;
 // a batch closed by that deadline is counted in timeout_batches.
+// setInFlight(n) (before start(); default 1 = the reference's single consumer, :79) runs n consumer threads on
+// the one queue, so that batch i+1 is packed and crosses PCIe while batch i computes (the engine's two transfer
+// slots); batches then complete concurrently and the counters count each of them as before.
 #pragma once
 #include <atomic>
 #include <chrono>
@@ -47,16 +50,19 @@ class BatchProcessor {
   ~BatchProcessor() { stop(); }
 
   void setFillWait(bool on) { fill_wait_ = on; }
+  void setInFlight(int n) { in_flight_ = n < 1 ? 1 : n; }
 
   void start() {
     if (running_.exchange(true)) return;
-    consumer_ = std::thread([this] { consume(); });
+    for (int i = 0; i < in_flight_; ++i) consumers_.emplace_back([this] { consume(); });
   }
 
   void stop() {
     running_ = false;
     cv_.notify_all();
-    if (consumer_.joinable()) consumer_.join();
+    for (auto& t : consumers_)
+      if (t.joinable()) t.join();
+    consumers_.clear();
     std::deque<Pending> left;
     {
       std::lock_guard<std::mutex> g(mu_);
@@ -143,7 +149,8 @@ class BatchProcessor {
   std::deque<Pending> queue_;
   std::mutex mu_;
   std::condition_variable cv_;
-  std::thread consumer_;
+  std::vector<std::thread> consumers_;
+  int in_flight_ = 1;
   std::atomic<bool> running_{false};
   std::atomic<int64_t> total_requests_{0};
   mutable std::mutex metrics_mu_;

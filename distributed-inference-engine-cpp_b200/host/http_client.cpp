@@ -28,8 +28,9 @@ bool send_all(int fd, const char* p, size_t n) {
   return true;
 }
 
-// Reads one response (status line, headers, Content-Length body).  `fresh_bytes` says whether anything arrived at
-// all: a keep-alive connection the peer closed while idle fails before the first byte and may be retried.
+// Reads one response (status line, headers, Content-Length body).  `got_bytes` says whether the request may NOT be
+// retried: a keep-alive connection the peer closed while idle fails with EOF / reset before the first byte (false,
+// retry once on a fresh socket); bytes received, or a read timeout, are final (true).
 bool read_response(int fd, ClientResult& r, bool& got_bytes, bool& keep_alive) {
   std::string buf;
   size_t header_end = std::string::npos;
@@ -38,7 +39,14 @@ bool read_response(int fd, ClientResult& r, bool& got_bytes, bool& keep_alive) {
   while (header_end == std::string::npos) {
     ssize_t k = ::recv(fd, tmp, sizeof tmp, 0);
     if (k < 0 && errno == EINTR) continue;
-    if (k <= 0) { r.error = k == 0 ? "connection closed by worker" : (errno == EAGAIN || errno == EWOULDBLOCK ? "read timeout" : std::strerror(errno)); return false; }
+    if (k <= 0) {
+      const bool timed_out = k < 0 && (errno == EAGAIN || errno == EWOULDBLOCK);
+      r.error = k == 0 ? "connection closed by worker" : (timed_out ? "read timeout" : std::strerror(errno));
+      // a read timeout is a final answer (the worker HAS the request: sending it again would run the inference twice
+      // and delay the breaker's failure count); only EOF / reset before the first byte marks a stale pooled socket
+      if (timed_out) got_bytes = true;
+      return false;
+    }
     got_bytes = true;
     buf.append(tmp, size_t(k));
     header_end = buf.find("\r\n\r\n");

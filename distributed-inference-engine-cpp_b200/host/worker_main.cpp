@@ -4,6 +4,7 @@
 // POST /infer -> handleInfer, exceptions -> HTTP 500 {"error": what}; GET /health -> getHealth.
 // Build with -DWORKER_FAKE_ENGINE for a CPU-only binary whose "engine" returns a checksum row per sample
 // (used by the host-side tests of the JSON contract; never by the product).
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
@@ -51,8 +52,14 @@ int main(int argc, char** argv) {
   Worker worker(node_id, port, model_path);
   if (const char* fw = std::getenv("B200RN_FILL_WAIT"))
     if (fw[0] == '1') worker.setFillWait(true);      // optional fill-or-timeout batching (changes /health counters)
+  if (const char* nf = std::getenv("B200RN_INFLIGHT"))
+    if (std::atoi(nf) > 1) worker.setInFlight(std::atoi(nf));   // optional: batch i+1 is packed and transferred while batch i computes
 
-  mini_http::Server server;
+  mini_http::Server server(std::getenv("B200RN_HTTP_THREADS") ? std::atoi(std::getenv("B200RN_HTTP_THREADS")) : 0);
+  if (const char* to = std::getenv("B200RN_HTTP_TIMEOUTS")) {      // "<read seconds>,<idle seconds>" (defaults 5, 30)
+    int rd = 5, idle = 30;
+    if (std::sscanf(to, "%d,%d", &rd, &idle) >= 1) server.set_timeouts(rd > 0 ? rd : 5, idle > 0 ? idle : 30);
+  }
   server.Post("/infer", [&worker](const mini_http::Request& req, mini_http::Response& res) {
     try {
       // B200RN_FAST_JSON=0 forces the reference's parse-then-convert path for every body (A/B and tests)

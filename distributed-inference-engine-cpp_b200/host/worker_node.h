@@ -134,6 +134,13 @@ class WorkerNodeT {
 
   Engine& engine() { return engine_; }
   void setFillWait(bool on) { batcher_.setFillWait(on); }
+  // n batches in flight (n consumer threads; the engine's batchPredict must accept concurrent calls -- the B200
+  // InferenceEngine gives each its own transfer slot).  Call before serving: queued requests would be failed.
+  void setInFlight(int n) {
+    batcher_.stop();
+    batcher_.setInFlight(n);
+    batcher_.start();
+  }
 
  private:
   std::vector<InferenceResponse> processBatch(const std::vector<InferenceRequest>& requests) {

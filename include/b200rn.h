@@ -205,6 +205,11 @@ size_t b200rn_lru_misses(const b200rn_lru_t* c);
  * x+1.  out[0..4] = total_requests, total_batches, timeout_batches, full_batches, wrong answers. */
 void b200rn_batch_selftest(int max_batch, int timeout_ms, int callback_ms, int submitters, int per_thread,
                            long long* out, double* avg_batch);
+/* The same with the two optional policies of this repository's BatchProcessor (host/batch_processor.h; neither
+ * exists in the reference): fill_wait = wait up to timeout_ms for a batch to fill (first half),
+ * in_flight = consumer threads (second half: two batches in flight).  out[5] = most callbacks seen running at once. */
+void b200rn_batch_selftest2(int max_batch, int timeout_ms, int callback_ms, int submitters, int per_thread, int fill_wait,
+                            int in_flight, long long* out, double* avg_batch);
 
 #ifdef __cplusplus
 }

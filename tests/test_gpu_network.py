@@ -219,6 +219,40 @@ def test_double_buffered_submit(tmp_path):
     eng.close()
 
 
+def test_two_threads_in_flight_on_one_handle(tmp_path):
+    """b200rn_infer from two threads at once (what the worker's two batch consumers do with B200RN_INFLIGHT=2): each
+    call owns one transfer slot, results are the bits a lone call gives, over many rounds and ragged batches; a
+    batch above max_batch (which needs both slots) in the middle of it still comes out right."""
+    import threading
+    p = str(tmp_path / "s.onnx")
+    gen.write_model(p, "small64", seed=8)
+    eng = pkg.Engine(p, mode="fp16", max_batch=8)
+    rs = np.random.RandomState(5)
+    per = 3 * 64 * 64
+    batches = [[rs.randn(per if (i + j) % 3 else 100).astype(np.float32) for j in range(1 + (i * 3) % 8)] for i in range(12)]
+    batches.append([rs.randn(per).astype(np.float32) for _ in range(19)])            # > max_batch: both slots
+    want = [np.stack(eng.batch_predict(b)) for b in batches]
+    errors = []
+
+    def worker(offset):
+        try:
+            for rnd in range(6):
+                for k in range(offset, len(batches), 2):
+                    got = np.stack(eng.batch_predict(batches[k]))
+                    if not np.array_equal(got, want[k]):
+                        errors.append((offset, rnd, k, float(np.abs(got - want[k]).max())))
+        except Exception as e:                                                       # noqa: BLE001
+            errors.append(repr(e))
+
+    ts = [threading.Thread(target=worker, args=(o,)) for o in (0, 1)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    eng.close()
+    assert not errors, errors[:5]
+
+
 def test_graph_replay_equals_eager(tmp_path):
     """The engine runs a (batch, slot) combination eagerly the first time, captures a CUDA graph the second time and
     replays it afterwards: all three must give the same bits for the same data, per batch size, with other batch

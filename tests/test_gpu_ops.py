@@ -23,6 +23,21 @@ def test_conv2d(dtype, name, kw, monkeypatch):
             assert r[key]["viol"] == 0, (name, key, r[key])
 
 
+SIMT_CASES = [c for c in gh.CONV_CASES if c[0] in ("1x1 s1 64->64 @56 B2", "3x3 s1 128->128 @28 B5", "1x1 s2 256->512 @56 B2",
+                                                   "1x1 64->256 @14 res+dual", "3x3 s2 512->512 @14 B33")]
+
+
+@pytest.mark.parametrize("name,kw", SIMT_CASES, ids=[c[0] for c in SIMT_CASES])
+def test_conv2d_fp32_cuda_core_kernel(name, kw, monkeypatch):
+    """B200RN_EXACT_SIMT=1: the fp32 CUDA-core conv (round 1's exact path; the stem and the FC still run on it)."""
+    monkeypatch.setenv("B200RN_EXACT_SIMT", "1")
+    r = gh.conv_case(0, **kw)
+    assert r["rc"] == 0, r["msg"]
+    for key in ("out", "act"):
+        if key in r:
+            assert r[key]["viol"] == 0, (name, key, r[key])
+
+
 SINGLE_SM_CASES = [c for c in gh.CONV_CASES if "dual-M" in c[0] or c[0].startswith("pair")]
 
 

@@ -340,3 +340,26 @@ def test_batch_processor_behaviour_matches_reference():
         avg2 = C.c_double()
         ref.ref_batch_run(32, 20, 30, 64, 1, out2, C.byref(avg2))
         assert out2[0] == 64 and out2[4] == 0 and out2[2] == 0 and out2[3] == out2[1] and 2 <= out2[1] < 64
+
+
+def test_batch_processor_fill_wait_and_two_in_flight():
+    """The two optional batching policies of SURVEY 8(f) rank 3 (neither is in the reference, both are off by default):
+    fill-or-timeout counts deadline batches in timeout_batches and full ones in full_batches; two consumer threads
+    run two callbacks at once and still answer every request correctly."""
+    out = (C.c_longlong * 6)()
+    avg = C.c_double()
+    # three requests, batch cap 8, 60 ms to fill: one batch of 3 closed by the deadline
+    lib.b200rn_batch_selftest2(8, 200, 1, 3, 1, 1, 1, out, C.byref(avg))
+    total, batches, timeout_b, full_b, wrong = list(out)[:5]
+    # (a loaded host may start a submitter thread late: then a second deadline batch, never a "full" one)
+    assert total == 3 and wrong == 0 and full_b == 0 and 1 <= timeout_b == batches <= 2 and abs(avg.value * batches - 3.0) < 1e-9
+    # eight requests fill the batch before the deadline: one full batch, no timeout batch
+    lib.b200rn_batch_selftest2(8, 2000, 1, 8, 1, 1, 1, out, C.byref(avg))
+    assert list(out)[:5] == [8, 1, 0, 1, 0]
+    # default policy, one consumer: never more than one callback at a time
+    lib.b200rn_batch_selftest2(4, 20, 20, 16, 2, 0, 1, out, C.byref(avg))
+    assert out[0] == 32 and out[4] == 0 and out[5] == 1
+    # two in flight: two callbacks overlap, all 32 answers right, batch accounting still adds up
+    lib.b200rn_batch_selftest2(4, 20, 20, 16, 2, 0, 2, out, C.byref(avg))
+    assert out[0] == 32 and out[4] == 0 and out[5] == 2
+    assert abs(avg.value * out[1] - 32) < 1e-6 and out[2] == 0 and out[3] == out[1]

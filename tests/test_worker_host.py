@@ -194,3 +194,41 @@ def test_octet_stream_side_channel_equals_json(worker_pair):
     assert r.status_code == 500 and "whole number of float32" in r.json()["error"]
     r = requests.post(url + "/infer", data=x.tobytes(), headers={"Content-Type": "application/octet-stream"}, timeout=5)
     assert r.status_code == 500 and "X-Request-Id" in r.json()["error"]
+
+
+def test_idle_and_stalled_connections_do_not_hold_request_threads():
+    """Two request threads, eight idle keep-alive connections and one peer stalled mid-header: a health probe is
+    still answered at once (threads bound requests, not connections), the stalled peer is dropped after the read
+    timeout, an idle connection is closed after the idle timeout, and a parked connection still serves its next
+    request."""
+    if not os.path.exists(FAKE):
+        pytest.skip("worker_node_fake not built (nlohmann/json.hpp not found)")
+    port = _free_port()
+    env = dict(os.environ, B200RN_HTTP_THREADS="2", B200RN_HTTP_TIMEOUTS="1,3")
+    proc = subprocess.Popen([FAKE, str(port), "worker_t", "unused.onnx"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, env=env)
+    url = "http://127.0.0.1:%d" % port
+    try:
+        for _ in range(100):
+            try:
+                requests.get(url + "/health", timeout=0.5)
+                break
+            except Exception:
+                time.sleep(0.05)
+        sessions = [requests.Session() for _ in range(8)]
+        for i, s in enumerate(sessions):        # each does one request and then sits idle with its connection open
+            assert s.post(url + "/infer", json={"request_id": "k%d" % i, "input_data": [float(i)]}, timeout=5).status_code == 200
+        stalled = socket.create_connection(("127.0.0.1", port))
+        stalled.sendall(b"POST /infer HTTP/1.1\r\nContent-Length: 10\r\n")     # never finishes its header block
+        t0 = time.time()
+        assert requests.get(url + "/health", timeout=2).status_code == 200
+        assert time.time() - t0 < 0.5
+        assert sessions[3].post(url + "/infer", json={"request_id": "again", "input_data": [3.0]}, timeout=5).json()["cached"] is True
+        stalled.settimeout(4)
+        assert stalled.recv(16) == b""                                             # dropped after ~1 s, not kept for ever
+        idle = socket.create_connection(("127.0.0.1", port))
+        idle.settimeout(8)
+        assert idle.recv(16) == b""                                                # closed after the 3 s idle timeout
+        assert requests.get(url + "/health", timeout=2).json()["total_requests"] == 9
+    finally:
+        proc.terminate()
+        proc.wait(timeout=5)
