@@ -423,7 +423,7 @@ def main():
             with open(os.path.join(ROOT, "profiles", "r2_conv_traffic.json")) as f:
                 tj = json.load(f)
             if (B == tj.get("batch", 256) and args.mode == tj.get("mode", "fp16") and tj.get("kernel_source_sha256") == kernel_source_hash()
-                    and tj.get("conv_launches_per_step") == len(conv)):
+                    and tj.get("conv_launches_per_step") == len(conv) + sum(1 for l in layers if l["kind"] == "Gemm")):   # the profile counts the FC's tensor-core launch too
                 traffic = tj["conv_dram_bytes_per_step"]
                 traffic_src = ("profiles/r2_conv_traffic.json (ncu dram__bytes_read+write, sum over the %d conv launches of one step; "
                                "kernel sources %s)" % (len(conv), tj["kernel_source_sha256"][:12]))

@@ -89,7 +89,7 @@ def launches(path, traffic_json=None):
             d.get("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", 0.0)))
     if traffic_json:
         import json
-        conv = [d for d in items if any(t in d["name"] for t in ("conv_umma", "conv_wide", "conv_tail", "halo", "stem7x7", "dualm"))]
+        conv = [d for d in items if any(t in d["name"] for t in ("conv_umma", "conv_wide", "conv_tail", "conv_pair", "halo", "stem7x7", "dualm"))]
         out = {"source": path.split("/")[-1], "conv_launches_per_step": len(conv),
                "conv_dram_bytes_per_step": sum(d.get("dram__bytes_read.sum", 0.0) + d.get("dram__bytes_write.sum", 0.0) for d in conv),
                "all_dram_bytes_per_step": sum(d.get("dram__bytes_read.sum", 0.0) + d.get("dram__bytes_write.sum", 0.0) for d in items),
