@@ -27,6 +27,7 @@ struct Tf32Params {
   int num_k_iters, cblks, kw, stride, pad;
   int bw, bh, bn, tiles_w, tiles_h, n_tiles, total_tiles, num_stages;
   int has_res, has_out, has_act, relu, act_relu;
+  int stg;                        // staging buffers per output (1, or 2 for the epilogue-bound layers: chunk c+1 is written while chunk c's store is still being read)
   int cout;                       // row pitch (floats) of the residual tensor
   int Ho, Wo, B;
   uint32_t rows, a_bytes;
@@ -79,9 +80,9 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int S = p.num_stages;
   uint8_t* pipe = smem;
-  uint8_t* outbuf = pipe + S * STAGE_BYTES;           // raw-output staging chunk (16 KB)
-  uint8_t* actbuf = outbuf + kChunkBytes;             // activated-output staging chunk (16 KB)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(actbuf + kChunkBytes);
+  uint8_t* outbuf = pipe + S * STAGE_BYTES;           // raw-output staging: p.stg chunks of 16 KB
+  uint8_t* actbuf = outbuf + p.stg * kChunkBytes;     // activated-output staging: p.stg chunks of 16 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(actbuf + p.stg * kChunkBytes);
   uint64_t* full_bar = bars;                  // [S]  TMA -> transform warps
   uint64_t* xf_bar = full_bar + S;            // [S]  transform warps -> MMA (4 warp arrivals)
   uint64_t* empty_bar = xf_bar + S;           // [S]  MMA -> TMA
@@ -223,8 +224,8 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     const int sw = row & 7;
     const bool store_thread = (ew == 0 && lane == 0);
     const uint32_t lane_addr = tmem_base + (uint32_t(q4 * 32) << 16);
-    const uint32_t out_row = smem_u32(outbuf) + uint32_t(row) * 128u;
-    const uint32_t act_row = smem_u32(actbuf) + uint32_t(row) * 128u;
+    const uint32_t out_row0 = smem_u32(outbuf) + uint32_t(row) * 128u;
+    const uint32_t act_row0 = smem_u32(actbuf) + uint32_t(row) * 128u;
     int cc = 0;
     uint32_t mchunk = 0;                        // running MAIN chunk counter (same sequence as the MMA thread's)
     for (int i = 0; i < my_tiles; ++i) {
@@ -236,6 +237,13 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       const int ox = w0 + px, oy = h0 + py, on = n0 + pn;
       const bool in_range = row < int(p.rows) && ox < p.Wo && oy < p.Ho && on < p.B;
       const float* res_px = p.residual + ((size_t(on) * p.Ho + oy) * p.Wo + ox) * size_t(p.cout);
+      // residual of the tile's first chunk: requested now, needed only after the whole K loop
+      float4 rv[4], rn[4];
+      if (p.has_res) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          rv[k] = in_range ? __ldg(reinterpret_cast<const float4*>(res_px + col0 + g * 16) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
       // ---- level 2 of the accumulation: every finished MAIN chunk is added into registers ----
       float sum[kChunks * 16];
 #pragma unroll
@@ -264,13 +272,13 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         const int ch0 = c * 32 + g * 16;            // first of this thread's 16 channels within the N tile
         uint32_t d1[16];
         tmem_ld_32x32b_x16(lane_addr + uint32_t(2 + buf) * BLOCK_N + uint32_t(ch0), d1);
-        float4 bv[4], rv[4];
+        float4 bv[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) bv[k] = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + ch0) + k);
-        if (p.has_res) {
+        if (p.has_res && c + 1 < kChunks) {       // the next chunk's residual, one chunk ahead
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            rv[k] = in_range ? __ldg(reinterpret_cast<const float4*>(res_px + col0 + ch0) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+            rn[k] = in_range ? __ldg(reinterpret_cast<const float4*>(res_px + col0 + ch0 + 32) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
         tmem_ld_wait();
         if (c == kChunks - 1) {             // accumulator fully read: hand it back to the MMA thread
@@ -278,8 +286,15 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           __syncwarp();
           if (lane == 0) mbar_arrive(smem_u32(&lo_empty[buf]));
         }
-        if (store_thread && cc > 0) tma_store_wait_read();   // the previous chunk's stores have read both staging buffers
+        // the staging buffers about to be written have been read by their stores: all of them, or -- with two buffers per
+        // output -- all but the previous chunk's
+        if (store_thread && cc > 0) {
+          if (p.stg == 2) tma_store_wait_read_pending<1>();
+          else tma_store_wait_read();
+        }
         asm volatile("bar.sync 1, 256;" ::: "memory");
+        const uint32_t sb = (p.stg == 2) ? uint32_t(cc & 1) * kChunkBytes : 0u;
+        const uint32_t out_row = out_row0 + sb, act_row = act_row0 + sb;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           float v[4];
@@ -303,9 +318,13 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         fence_proxy_async_smem();
         asm volatile("bar.sync 1, 256;" ::: "memory");
         if (store_thread) {
-          if (p.has_out) tma_store_4d(&tmOut, smem_u32(outbuf), col0 + c * 32, w0, h0, n0);
-          if (p.has_act) tma_store_4d(&tmAct, smem_u32(actbuf), col0 + c * 32, w0, h0, n0);
+          if (p.has_out) tma_store_4d(&tmOut, smem_u32(outbuf) + sb, col0 + c * 32, w0, h0, n0);
+          if (p.has_act) tma_store_4d(&tmAct, smem_u32(actbuf) + sb, col0 + c * 32, w0, h0, n0);
           tma_store_commit();
+        }
+        if (p.has_res) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) rv[k] = rn[k];
         }
       }
     }

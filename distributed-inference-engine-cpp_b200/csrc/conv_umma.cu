@@ -9,13 +9,23 @@
 //   (and, for stride 2, element-strided) position.  Out-of-bounds coordinates are zero-filled by
 //   the TMA unit, which *is* the conv's zero padding.  The M tile is therefore a spatial patch
 //   bw x bh of bn images (bw*bh*bn <= 128), chosen per layer and batch to fill the 128-row MMA.
-// * The 7x7/2 stem (3 input channels) uses a 5-D overlapping-stride view of a zero-framed
-//   [B,230,232,4] input: one K-block per filter row = 8 consecutive pixels x 4 channels = 64 bytes
-//   (SWIZZLE_64B), so K = 7 x 32 with the 8th pixel / 4th channel multiplied by zero weights.
-// * Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread
-//   tcgen05.mma issuer, warps 2-5 = epilogue (TMEM -> registers -> swizzled smem -> TMA store).
-//   One output tile per CTA; shared memory is sized so two CTAs share an SM and one CTA's
-//   epilogue overlaps the other's main loop.
+// * The 7x7/2 stem (3 input channels, stored as 4) reads a zero-framed [B, H+6, Wp, 4] input: stem7x7_kernel fetches one
+//   37-row patch per 8x16-output tile and feeds the MMA through un-swizzled overlapping descriptors (the sliding
+//   window is the descriptor's 16-byte LBO); the generic kernel's 5-D overlapping-stride view (one 64-byte K block
+//   per filter row, SWIZZLE_64B) remains as B200RN_STEM_V2=0 and for the allocation-free entry point.
+// * Every kernel here is persistent (one CTA -- or one CTA of a 2-CTA cluster -- per SM walking a static tile list)
+//   and warp-specialised: warp 0 = TMA producer, warp 1 = TMEM allocation + the single tcgen05.mma-issuing thread,
+//   then 8 or 16 epilogue warps (TMEM -> registers -> swizzled shared memory -> TMA store), plus kernel-specific
+//   roles (operand-transform warps, store warp, residual producer).  Accumulators are double-buffered in TMEM so
+//   a tile's epilogue overlaps the next tile's MMAs.  Kernels in this file and its includes:
+//     conv_umma_kernel     general implicit GEMM, compile-time epilogue variants, stationary small weight slabs
+//     conv3x3_halo_kernel  3x3/s1 on 64/128 channels, one halo patch per tile, row-shifted A descriptors
+//     stem7x7_kernel       the stem (above)
+//     conv_dualm_kernel    two M tiles per weight tile (large K, N = 128)
+//     conv_pair_kernel     conv_pair.cuh: one 256 x 256 tile per 2-CTA cluster, tcgen05.mma.cta_group::2
+//     conv_wide_kernel     conv_wide.cuh: block-ending 1x1 convs, chunk rings, store + residual warps, two-input form
+//     conv_tail_kernel     conv_tail.cuh: block-ending 1x1 conv + the next block's 1x1 conv in one launch
+//     conv_tf32x3_kernel   conv_tf32.cuh: exact mode, fp32 storage, 3 x TF32 split products, two-level accumulation
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -2402,7 +2412,11 @@ Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g, const float* in, const fl
   p.residual = static_cast<const float*>(e.residual);
   if (p.has_act && (!e.act_scale || !e.act_shift)) { delete pl; return failmsg("activated output needs scale and shift"); }
   const uint32_t stage_bytes = 2u * kTileM * 128 + 2u * uint32_t(pl->block_n) * 128;
-  const uint32_t fixed = 1024u + 2 * kChunkBytes + 8u * (3 * 8 + 4) + 64;
+  // epilogue-bound layers (a residual to add, or two outputs to write; their K is short) double-buffer the output
+  // staging and give up an operand stage for it; B200RN_T32_STG=1/2 forces either
+  const char* stg_env = std::getenv("B200RN_T32_STG");
+  p.stg = stg_env ? (std::atoi(stg_env) == 2 ? 2 : 1) : ((p.has_res || (p.has_out && p.has_act)) ? 2 : 1);
+  const uint32_t fixed = 1024u + 2u * uint32_t(p.stg) * kChunkBytes + 8u * (3 * 8 + 8) + 64;
   p.num_stages = std::max(2, std::min(8, int((227u * 1024 - fixed) / stage_bytes)));
   pl->smem_bytes = fixed + uint32_t(p.num_stages) * stage_bytes;
   pl->grid = std::min(p.total_tiles, sm_count());
