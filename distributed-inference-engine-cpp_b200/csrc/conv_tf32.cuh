@@ -15,19 +15,24 @@
 // buffers and the epilogue warps add every finished chunk into fp32 REGISTERS (N/2 per thread) with properly rounded
 // adds while the next chunk is being multiplied.  LO is 2^-11 of MAIN, its truncation error is negligible, and it stays
 // in tensor memory for the whole K (double-buffered across tiles).  v = registers + LO + bias.
-// Epilogue (8 warps): bias, ReLU, residual (read straight from global memory, 128 contiguous bytes per thread), raw and/or
-// BN-ReLU'd output staged in swizzled shared memory and written by TMA stores, 32 channels (128 bytes) per chunk.
+// Epilogue (two groups of 8 warps on alternating 32-channel chunks): bias, ReLU, residual (read straight from global
+// memory one chunk ahead, 64 contiguous bytes per thread), raw and/or BN-ReLU'd output staged in swizzled shared memory
+// (one buffer per output and group) and written by TMA stores, 32 channels (128 bytes) per chunk.
+// The 7x7/2 stem (3 channels stored as 4) reads a zero-framed fp32 input through a 5-D overlapping view: K block ky is the
+// 8 pixels x 4 channels = 32 contiguous floats at frame row 2y + ky, pixel 2x (the 8th pixel meets zero weights), so the
+// stem is 7 K blocks of the same pipeline.
 // K is ordered (ky, kx, cin) in blocks of 32 channels; the operand box is {32 ch, bw, bh, bn} fp32 with the conv's
 // stride as element stride and TMA zero fill as padding, exactly like the 16-bit kernels.
 constexpr int kT32XfWarps = 4;
 constexpr int kT32ChunkBlocks = 4;          // K blocks (of 32 channels) per MAIN chunk
-constexpr int kT32Threads = 64 + kT32XfWarps * 32 + kEpiThreads;     // TMA, MMA, 4 transform warps, 8 epilogue warps
+constexpr int kT32EpiWarps = 16;
+constexpr int kT32Threads = 64 + kT32XfWarps * 32 + kT32EpiWarps * 32;   // TMA, MMA, 4 transform warps, 2 x 8 epilogue warps
 
 struct Tf32Params {
   int num_k_iters, cblks, kw, stride, pad;
+  int stem;                       // 7x7/2 stem on a zero-framed 4-channel input: K block ky = 8 pixels x 4 channels of frame row 2y + ky
   int bw, bh, bn, tiles_w, tiles_h, n_tiles, total_tiles, num_stages;
   int has_res, has_out, has_act, relu, act_relu;
-  int stg;                        // staging buffers per output (1, or 2 for the epilogue-bound layers: chunk c+1 is written while chunk c's store is still being read)
   int cout;                       // row pitch (floats) of the residual tensor
   int Ho, Wo, B;
   uint32_t rows, a_bytes;
@@ -70,6 +75,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                    const __grid_constant__ CUtensorMap tmWlo, const __grid_constant__ CUtensorMap tmOut,
                    const __grid_constant__ CUtensorMap tmAct, const Tf32Params p) {
   constexpr int kChunks = BLOCK_N / 32;               // 32 fp32 channels = one 128-byte staging row
+  constexpr int kGroupChunks = kChunks / 2;           // chunks per epilogue group and tile
   constexpr uint32_t A_BYTES = kTileM * 128;          // 128 rows x 32 fp32
   constexpr uint32_t B_BYTES = BLOCK_N * 128;         // one of the two weight tiles
   constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;   // A_hi | A_lo | W_hi | W_lo
@@ -80,16 +86,16 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int S = p.num_stages;
   uint8_t* pipe = smem;
-  uint8_t* outbuf = pipe + S * STAGE_BYTES;           // raw-output staging: p.stg chunks of 16 KB
-  uint8_t* actbuf = outbuf + p.stg * kChunkBytes;     // activated-output staging: p.stg chunks of 16 KB
-  uint64_t* bars = reinterpret_cast<uint64_t*>(actbuf + p.stg * kChunkBytes);
+  uint8_t* outbuf = pipe + S * STAGE_BYTES;                       // raw-output staging: one 16 KB chunk per epilogue group
+  uint8_t* actbuf = outbuf + (p.has_out ? 2 * kChunkBytes : 0);   // activated-output staging: one chunk per group
+  uint64_t* bars = reinterpret_cast<uint64_t*>(actbuf + (p.has_act ? 2 * kChunkBytes : 0));
   uint64_t* full_bar = bars;                  // [S]  TMA -> transform warps
   uint64_t* xf_bar = full_bar + S;            // [S]  transform warps -> MMA (4 warp arrivals)
   uint64_t* empty_bar = xf_bar + S;           // [S]  MMA -> TMA
   uint64_t* main_full = empty_bar + S;        // [2]  MMA -> epilogue: a MAIN chunk is complete
-  uint64_t* main_empty = main_full + 2;       // [2]  epilogue -> MMA (8 warp arrivals): chunk added into registers
+  uint64_t* main_empty = main_full + 2;       // [2]  epilogue -> MMA (16 warp arrivals): chunk added into registers
   uint64_t* lo_full = main_empty + 2;         // [2]  MMA -> epilogue: a tile's LO accumulator is complete
-  uint64_t* lo_empty = lo_full + 2;           // [2]  epilogue -> MMA (8 warp arrivals)
+  uint64_t* lo_empty = lo_full + 2;           // [2]  epilogue -> MMA (16 warp arrivals)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(lo_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -105,8 +111,8 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       mbar_init(smem_u32(&empty_bar[i]), 1);
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(smem_u32(&main_full[i]), 1); mbar_init(smem_u32(&main_empty[i]), kEpiWarps);
-      mbar_init(smem_u32(&lo_full[i]), 1); mbar_init(smem_u32(&lo_empty[i]), kEpiWarps);
+      mbar_init(smem_u32(&main_full[i]), 1); mbar_init(smem_u32(&main_empty[i]), kT32EpiWarps);
+      mbar_init(smem_u32(&lo_full[i]), 1); mbar_init(smem_u32(&lo_empty[i]), kT32EpiWarps);
     }
     fence_barrier_init();
   }
@@ -142,7 +148,8 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           const uint32_t dst = smem_u32(pipe + stage * STAGE_BYTES);
           const int tap = it / p.cblks, cb = it - tap * p.cblks;
           const int ky = tap / p.kw, kx = tap - ky * p.kw;
-          tma_load_4d(dst, &tmA, fb, cb * 32, w0 * p.stride - p.pad + kx, h0 * p.stride - p.pad + ky, n0);
+          if (p.stem) tma_load_5d(dst, &tmA, fb, 0, w0, it & 1, h0 + (it >> 1), n0);   // (32 elems, out col, row parity, row pair, image)
+          else tma_load_4d(dst, &tmA, fb, cb * 32, w0 * p.stride - p.pad + kx, h0 * p.stride - p.pad + ky, n0);
           tma_load_2d(dst + 2 * A_BYTES, &tmWhi, fb, it * 32, col0);
           tma_load_2d(dst + 2 * A_BYTES + B_BYTES, &tmWlo, fb, it * 32, col0);
           if (++stage == S) { stage = 0; phase ^= 1; }
@@ -216,17 +223,23 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       if (++stage == S) { stage = 0; phase ^= 1; }
     }
   } else {
-    // ===== epilogue: 8 warps; thread = one output pixel (TMEM lane) x 16 of a chunk's 32 channels =====
-    const int ew = warp - 2 - kT32XfWarps;
+    // ===== epilogue: two groups of 8 warps; group grp owns the 32-channel chunks grp, grp + 2, ... of every tile (its own
+    // staging buffers, named barrier and store thread), so two chunk chains are in flight per SM -- one chain at a time
+    // (TMEM load, residual, math, smem, proxy fence, barrier, TMA store, "store has read" wait) ran the residual layers at a
+    // third of the HBM rate.  thread = one output pixel (TMEM lane) x 16 of a chunk's 32 channels =====
+    const int ew = warp - 2 - kT32XfWarps;  // 0..15
+    const int grp = ew >> 3;
     const int q4 = warp & 3;                // TMEM lane quarter this warp may access
-    const int g = ew >> 2;                  // which half of every 32-channel chunk (0/1)
+    const int g = (ew & 7) >> 2;            // which half of every 32-channel chunk (0/1)
     const int row = q4 * 32 + lane;
     const int sw = row & 7;
-    const bool store_thread = (ew == 0 && lane == 0);
+    const bool store_thread = ((ew & 7) == 0 && lane == 0);
+    const int bar_id = 1 + grp;
     const uint32_t lane_addr = tmem_base + (uint32_t(q4 * 32) << 16);
-    const uint32_t out_row0 = smem_u32(outbuf) + uint32_t(row) * 128u;
-    const uint32_t act_row0 = smem_u32(actbuf) + uint32_t(row) * 128u;
-    int cc = 0;
+    const uint32_t out_stage = smem_u32(outbuf) + uint32_t(grp) * kChunkBytes;
+    const uint32_t act_stage = smem_u32(actbuf) + uint32_t(grp) * kChunkBytes;
+    const uint32_t out_row = out_stage + uint32_t(row) * 128u, act_row = act_stage + uint32_t(row) * 128u;
+    int cc = 0;                                 // this group's running chunk counter
     uint32_t mchunk = 0;                        // running MAIN chunk counter (same sequence as the MMA thread's)
     for (int i = 0; i < my_tiles; ++i) {
       int w0, h0, n0, col0;
@@ -236,30 +249,30 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       const int px = row % p.bw, py = (row / p.bw) % p.bh, pn = row / (p.bw * p.bh);
       const int ox = w0 + px, oy = h0 + py, on = n0 + pn;
       const bool in_range = row < int(p.rows) && ox < p.Wo && oy < p.Ho && on < p.B;
-      const float* res_px = p.residual + ((size_t(on) * p.Ho + oy) * p.Wo + ox) * size_t(p.cout);
-      // residual of the tile's first chunk: requested now, needed only after the whole K loop
-      float4 rv[4], rn[4];
+      const float* res_px = p.residual + ((size_t(on) * p.Ho + oy) * p.Wo + ox) * size_t(p.cout) + col0 + g * 16;
+      // residual of the group's first chunk: requested now, needed only after the whole K loop
+      float4 rv[4];
       if (p.has_res) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-          rv[k] = in_range ? __ldg(reinterpret_cast<const float4*>(res_px + col0 + g * 16) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+          rv[k] = in_range ? __ldg(reinterpret_cast<const float4*>(res_px + grp * 32) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
       // ---- level 2 of the accumulation: every finished MAIN chunk is added into registers ----
-      float sum[kChunks * 16];
+      float sum[kGroupChunks * 16];
 #pragma unroll
-      for (int k = 0; k < kChunks * 16; ++k) sum[k] = 0.f;
+      for (int k = 0; k < kGroupChunks * 16; ++k) sum[k] = 0.f;
       const int n_chunks = (p.num_k_iters + kT32ChunkBlocks - 1) / kT32ChunkBlocks;
       for (int kc = 0; kc < n_chunks; ++kc, ++mchunk) {
         const uint32_t mbuf = mchunk & 1;
         mbar_wait(smem_u32(&main_full[mbuf]), (mchunk >> 1) & 1);
         tc_fence_after();
 #pragma unroll
-        for (int c = 0; c < kChunks; ++c) {
+        for (int j = 0; j < kGroupChunks; ++j) {
           uint32_t d[16];
-          tmem_ld_32x32b_x16(lane_addr + mbuf * BLOCK_N + uint32_t(c * 32 + g * 16), d);
+          tmem_ld_32x32b_x16(lane_addr + mbuf * BLOCK_N + uint32_t((grp + 2 * j) * 32 + g * 16), d);
           tmem_ld_wait();
 #pragma unroll
-          for (int k = 0; k < 16; ++k) sum[c * 16 + k] += __uint_as_float(d[k]);
+          for (int k = 0; k < 16; ++k) sum[j * 16 + k] += __uint_as_float(d[k]);
         }
         tc_fence_before();
         __syncwarp();
@@ -268,40 +281,29 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       mbar_wait(smem_u32(&lo_full[buf]), (uint32_t(i) >> 1) & 1);
       tc_fence_after();
 #pragma unroll
-      for (int c = 0; c < kChunks; ++c, ++cc) {
+      for (int j = 0; j < kGroupChunks; ++j, ++cc) {
+        const int c = grp + 2 * j;
         const int ch0 = c * 32 + g * 16;            // first of this thread's 16 channels within the N tile
         uint32_t d1[16];
         tmem_ld_32x32b_x16(lane_addr + uint32_t(2 + buf) * BLOCK_N + uint32_t(ch0), d1);
         float4 bv[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) bv[k] = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + ch0) + k);
-        if (p.has_res && c + 1 < kChunks) {       // the next chunk's residual, one chunk ahead
-#pragma unroll
-          for (int k = 0; k < 4; ++k)
-            rn[k] = in_range ? __ldg(reinterpret_cast<const float4*>(res_px + col0 + ch0 + 32) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
         tmem_ld_wait();
-        if (c == kChunks - 1) {             // accumulator fully read: hand it back to the MMA thread
+        if (j == kGroupChunks - 1) {        // this warp's part of the LO accumulator is read: hand it back to the MMA thread
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(smem_u32(&lo_empty[buf]));
         }
-        // the staging buffers about to be written have been read by their stores: all of them, or -- with two buffers per
-        // output -- all but the previous chunk's
-        if (store_thread && cc > 0) {
-          if (p.stg == 2) tma_store_wait_read_pending<1>();
-          else tma_store_wait_read();
-        }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        const uint32_t sb = (p.stg == 2) ? uint32_t(cc & 1) * kChunkBytes : 0u;
-        const uint32_t out_row = out_row0 + sb, act_row = act_row0 + sb;
+        if (store_thread && cc > 0) tma_store_wait_read();   // the group's previous stores have read its staging buffers
+        asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           float v[4];
-          v[0] = sum[c * 16 + 4 * k + 0] + __uint_as_float(d1[4 * k + 0]) + bv[k].x;
-          v[1] = sum[c * 16 + 4 * k + 1] + __uint_as_float(d1[4 * k + 1]) + bv[k].y;
-          v[2] = sum[c * 16 + 4 * k + 2] + __uint_as_float(d1[4 * k + 2]) + bv[k].z;
-          v[3] = sum[c * 16 + 4 * k + 3] + __uint_as_float(d1[4 * k + 3]) + bv[k].w;
+          v[0] = sum[j * 16 + 4 * k + 0] + __uint_as_float(d1[4 * k + 0]) + bv[k].x;
+          v[1] = sum[j * 16 + 4 * k + 1] + __uint_as_float(d1[4 * k + 1]) + bv[k].y;
+          v[2] = sum[j * 16 + 4 * k + 2] + __uint_as_float(d1[4 * k + 2]) + bv[k].z;
+          v[3] = sum[j * 16 + 4 * k + 3] + __uint_as_float(d1[4 * k + 3]) + bv[k].w;
           if (p.relu) { v[0] = fmaxf(v[0], 0.f); v[1] = fmaxf(v[1], 0.f); v[2] = fmaxf(v[2], 0.f); v[3] = fmaxf(v[3], 0.f); }
           if (p.has_res) { v[0] += rv[k].x; v[1] += rv[k].y; v[2] += rv[k].z; v[3] += rv[k].w; }
           const uint32_t slot16 = uint32_t(((g * 4 + k) ^ sw) << 4);      // SWIZZLE_128B: 16-byte slot XOR (row mod 8)
@@ -315,16 +317,17 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             sts_u4(act_row + slot16, make_uint4(__float_as_uint(a[0]), __float_as_uint(a[1]), __float_as_uint(a[2]), __float_as_uint(a[3])));
           }
         }
-        fence_proxy_async_smem();
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (store_thread) {
-          if (p.has_out) tma_store_4d(&tmOut, smem_u32(outbuf) + sb, col0 + c * 32, w0, h0, n0);
-          if (p.has_act) tma_store_4d(&tmAct, smem_u32(actbuf) + sb, col0 + c * 32, w0, h0, n0);
-          tma_store_commit();
-        }
-        if (p.has_res) {
+        if (p.has_res && j + 1 < kGroupChunks) {       // the group's next chunk's residual (64 channels further on)
 #pragma unroll
-          for (int k = 0; k < 4; ++k) rv[k] = rn[k];
+          for (int k = 0; k < 4; ++k)
+            rv[k] = in_range ? __ldg(reinterpret_cast<const float4*>(res_px + (c + 2) * 32) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        fence_proxy_async_smem();
+        asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
+        if (store_thread) {
+          if (p.has_out) tma_store_4d(&tmOut, out_stage, col0 + c * 32, w0, h0, n0);
+          if (p.has_act) tma_store_4d(&tmAct, act_stage, col0 + c * 32, w0, h0, n0);
+          tma_store_commit();
         }
       }
     }

@@ -2337,6 +2337,19 @@ struct Tf32ConvPlan {
 bool tf32_conv_supported(const ConvGeom& g) {
   return g.Cin % 32 == 0 && g.Cout % 64 == 0 && g.kh == g.kw && (g.stride == 1 || g.stride == 2);
 }
+// the 7x7 / stride-2 / pad-3 stem on a 4-channel (3 padded) input of even height, read from a zero-framed copy
+bool tf32_stem_supported(const ConvGeom& g) {
+  return g.kh == 7 && g.kw == 7 && g.stride == 2 && g.pad == 3 && g.Cin == 4 && g.Cout % 64 == 0 && g.H % 2 == 0;
+}
+size_t tf32_stem_weight_elems(int Cout) { return size_t(Cout) * 7 * 32; }
+// [Cout][7][7][4] -> [Cout][ky 0..6][kx 0..7][c 0..3] with kx = 7 zero
+void tf32_pack_stem_weights(const float* w, int Cout, float* dst) {
+  for (int o = 0; o < Cout; ++o)
+    for (int ky = 0; ky < 7; ++ky)
+      for (int kx = 0; kx < 8; ++kx)
+        for (int c = 0; c < 4; ++c)
+          dst[((size_t(o) * 7 + ky) * 8 + kx) * 4 + c] = kx < 7 ? w[((size_t(o) * 7 + ky) * 7 + kx) * 4 + c] : 0.f;
+}
 
 void tf32_split_weights(const float* w, size_t n, float* hi, float* lo) {
   for (size_t i = 0; i < n; ++i) {
@@ -2383,12 +2396,14 @@ static bool encode_act_f32(CUtensorMap* m, const void* base, int B, int H, int W
 }
 
 Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g, const float* in, const float* w_hi, const float* w_lo, const Epilogue& e,
-                                    char* err, size_t errcap) {
+                                    char* err, size_t errcap, int stem) {
   auto failmsg = [&](const std::string& m) -> Tf32ConvPlan* {
     if (err && errcap) std::snprintf(err, errcap, "%s", m.c_str());
     return nullptr;
   };
-  if (!tf32_conv_supported(g)) return failmsg("3xTF32 conv needs Cin % 32 == 0, Cout % 64 == 0, a square filter and stride 1 or 2");
+  if (stem ? !tf32_stem_supported(g) : !tf32_conv_supported(g))
+    return failmsg(stem ? "3xTF32 stem needs a 7x7/2 pad-3 conv on a 4-channel input of even height with Cout % 64 == 0"
+                        : "3xTF32 conv needs Cin % 32 == 0, Cout % 64 == 0, a square filter and stride 1 or 2");
   if (e.pre_scale || e.tail_out || e.in_b || e.out_f32 || e.pool_fused) return failmsg("3xTF32 conv has no prologue / tail / second input / fp32-row / pool form");
   if (!e.out && !e.out_act) return failmsg("conv with no output");
   auto pl = new Tf32ConvPlan();
@@ -2402,8 +2417,9 @@ Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g, const float* in, const fl
   p.tiles_w = (g.Wo + bw - 1) / bw; p.tiles_h = (g.Ho + bh - 1) / bh;
   p.n_tiles = g.Cout / pl->block_n;
   p.total_tiles = p.tiles_w * p.tiles_h * ((g.B + bn - 1) / bn) * p.n_tiles;
-  p.cblks = g.Cin / 32; p.kw = g.kw; p.stride = g.stride; p.pad = g.pad;
-  p.num_k_iters = g.kh * g.kw * p.cblks;
+  p.stem = stem;
+  p.cblks = stem ? 1 : g.Cin / 32; p.kw = g.kw; p.stride = g.stride; p.pad = g.pad;
+  p.num_k_iters = stem ? 7 : g.kh * g.kw * p.cblks;
   p.rows = uint32_t(bw * bh * bn); p.a_bytes = p.rows * 128u;
   p.has_res = e.residual != nullptr; p.has_out = e.out != nullptr; p.has_act = e.out_act != nullptr;
   p.relu = e.relu; p.act_relu = e.act_relu;
@@ -2412,17 +2428,27 @@ Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g, const float* in, const fl
   p.residual = static_cast<const float*>(e.residual);
   if (p.has_act && (!e.act_scale || !e.act_shift)) { delete pl; return failmsg("activated output needs scale and shift"); }
   const uint32_t stage_bytes = 2u * kTileM * 128 + 2u * uint32_t(pl->block_n) * 128;
-  // epilogue-bound layers (a residual to add, or two outputs to write; their K is short) double-buffer the output
-  // staging and give up an operand stage for it; B200RN_T32_STG=1/2 forces either
-  const char* stg_env = std::getenv("B200RN_T32_STG");
-  p.stg = stg_env ? (std::atoi(stg_env) == 2 ? 2 : 1) : ((p.has_res || (p.has_out && p.has_act)) ? 2 : 1);
-  const uint32_t fixed = 1024u + 2u * uint32_t(p.stg) * kChunkBytes + 8u * (3 * 8 + 8) + 64;
+  // staging: one 16 KB chunk per output and epilogue group
+  const uint32_t fixed = 1024u + 2u * uint32_t(p.has_out + p.has_act) * kChunkBytes + 8u * (3 * 8 + 8) + 64;
   p.num_stages = std::max(2, std::min(8, int((227u * 1024 - fixed) / stage_bytes)));
   pl->smem_bytes = fixed + uint32_t(p.num_stages) * stage_bytes;
   pl->grid = std::min(p.total_tiles, sm_count());
   std::string msg;
-  bool ok = encode_act_f32(&pl->tmA, in, g.B, g.H, g.W, g.Cin, bw, bh, bn, g.stride, msg);
-  const uint64_t K = uint64_t(g.kh) * g.kw * g.Cin;
+  bool ok;
+  if (stem) {
+    // 5-D overlapping view of the zero-framed input [B, Hp, Wp, 4] fp32 (image at (3,3)):
+    //   d0 = 32 floats (8 px x 4 ch), d1 = output column (2 px = 32 B apart), d2 = row parity, d3 = row pair, d4 = image
+    const int Hp = stem_Hp(g.H), Wp = stem_Wp(g.W);
+    const uint64_t rowpitch = uint64_t(Wp) * 4 * 4;
+    uint64_t dims[5] = {32, uint64_t(g.Wo), 2, uint64_t(Hp / 2), uint64_t(g.B)};
+    uint64_t str[4] = {32, rowpitch, 2 * rowpitch, uint64_t(Hp) * rowpitch};
+    uint32_t box[5] = {32, uint32_t(bw), 1, uint32_t(bh), uint32_t(bn)};
+    uint32_t es[5] = {1, 1, 1, 1, 1};
+    ok = encode_f32(&pl->tmA, 5, in, dims, str, box, es, msg);
+  } else {
+    ok = encode_act_f32(&pl->tmA, in, g.B, g.H, g.W, g.Cin, bw, bh, bn, g.stride, msg);
+  }
+  const uint64_t K = stem ? uint64_t(7 * 32) : uint64_t(g.kh) * g.kw * g.Cin;
   uint64_t wd[2] = {K, uint64_t(g.Cout)};
   uint64_t ws[1] = {K * 4};
   uint32_t wb[2] = {32, uint32_t(pl->block_n)};

@@ -146,7 +146,7 @@ struct b200rn {
   uint8_t* arena = nullptr;
   size_t arena_bytes = 0;
   std::vector<size_t> toff;       // byte offset of each tensor in the arena (sized for max_batch)
-  void* stem_frame = nullptr;     // zero-bordered [max_batch, Hp, Wp, 4] input frame (16-bit modes)
+  void* stem_frame = nullptr;     // zero-bordered [max_batch, Hp, Wp, 4] input frame (tensor-core stem, every mode)
   int stem_tensor = -1;
   cudaStream_t s_h2d = nullptr, s_compute = nullptr, s_d2h = nullptr;
   Slot slot[2];
@@ -304,6 +304,23 @@ struct b200rn {
           D.fc_cout_pad = Npad;
           CK(cudaMalloc(&D.fc_in16, size_t(max_batch) * L.Cin * 2));
           dl[size_t(plan.tensors[size_t(L.in)].def_layer)].gap_out16 = D.fc_in16;
+        } else if (L.kind == LayerKind::Conv && dt == DType::F32 && exact_tf32_enabled() && L.in_b < 0 && L.in2 < 0 &&
+                   L.pre_scale.empty() && L.tail_out < 0 && !L.fused_pool &&
+                   plan.layers[size_t(plan.tensors[size_t(L.in)].def_layer)].kind == LayerKind::InputXform &&
+                   plan.tensors[size_t(L.in)].Cpad == 4 &&
+                   tf32_stem_supported(ConvGeom{1, plan.tensors[size_t(L.in)].H, plan.tensors[size_t(L.in)].W, 4, 0, 0, L.Cout, L.kh, L.kw,
+                                                L.stride, L.pad})) {
+          // exact mode, the stem on the tensor cores: zero-framed fp32 input, weights [Cout][7][8][4] split into hi / lo
+          std::vector<float> packed(tf32_stem_weight_elems(L.Cout));
+          tf32_pack_stem_weights(L.weight.data(), L.Cout, packed.data());
+          std::vector<float> hi(packed.size()), lo(packed.size());
+          tf32_split_weights(packed.data(), packed.size(), hi.data(), lo.data());
+          D.w = upload(hi);
+          D.w_lo = upload(lo);
+          D.tf32 = true;
+          D.stem = 1;
+          D.weight_bytes = double(hi.size()) * 8;
+          stem_tensor = L.in;
         } else if (L.kind == LayerKind::Conv && dt == DType::F32 && exact_tf32_enabled() && L.in_b < 0 &&
                    L.pre_scale.empty() && L.tail_out < 0 && !L.fused_pool &&
                    tf32_conv_supported(ConvGeom{1, 1, 1, L.Cin, 1, 1, L.Cout, L.kh, L.kw, L.stride, L.pad})) {
@@ -332,7 +349,7 @@ struct b200rn {
     }
     if (stem_tensor >= 0) {
       const PlanTensor& t = plan.tensors[size_t(stem_tensor)];
-      size_t bytes = size_t(max_batch) * stem_Hp(t.H) * stem_Wp(t.W) * 4 * 2;
+      size_t bytes = size_t(max_batch) * stem_Hp(t.H) * stem_Wp(t.W) * 4 * dtype_size(dt);
       CK(cudaMalloc(&stem_frame, bytes));
       CK(cudaMemset(stem_frame, 0, bytes));
     }
@@ -407,7 +424,7 @@ struct b200rn {
           Tf32ConvPlan*& tp = D.tf32_plans[B];
           if (!tp) {
             char msg[512] = {0};
-            tp = tf32_conv_plan_create(g, static_cast<const float*>(tptr(L.in)), static_cast<const float*>(D.w), D.w_lo, e, msg, sizeof msg);
+            tp = tf32_conv_plan_create(g, static_cast<const float*>(tptr(L.in)), static_cast<const float*>(D.w), D.w_lo, e, msg, sizeof msg, D.stem);
             if (!tp) { D.tf32_plans.erase(B); throw CudaFail{fmt("layer '%s': %s", L.name.c_str(), msg)}; }
           }
           CK(launch_conv_tf32(tp, s));

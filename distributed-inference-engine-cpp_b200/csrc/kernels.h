@@ -112,8 +112,13 @@ struct Tf32ConvPlan;
 bool tf32_conv_supported(const ConvGeom& g);
 // w: [Cout][kh][kw][Cin] fp32 -> hi (low 13 mantissa bits cleared) and lo (w - hi, cut the same way)
 void tf32_split_weights(const float* w, size_t n, float* hi, float* lo);
+// stem != 0: the 7x7/2 stem; `in` is then the zero-framed fp32 input [B, H + 6, Wp, 4] (image at (3,3)) and the weights are
+// packed by tf32_pack_stem_weights ([Cout][7][8][4]) before the split
 Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g, const float* in, const float* w_hi, const float* w_lo, const Epilogue& e,
-                                    char* err, size_t errcap);
+                                    char* err, size_t errcap, int stem = 0);
+bool tf32_stem_supported(const ConvGeom& g);
+size_t tf32_stem_weight_elems(int Cout);
+void tf32_pack_stem_weights(const float* w, int Cout, float* dst);
 void tf32_conv_plan_destroy(Tf32ConvPlan*);
 cudaError_t launch_conv_tf32(const Tf32ConvPlan* p, cudaStream_t s);
 
