@@ -1077,12 +1077,45 @@ int b200rn_conv1x1_two_input(int dtype, const void* d_in, int B, int H, int W, i
 
 int b200rn_stem_conv(int dtype, const float* d_in_nchw, int B, int H, int W, const float* in_scale,
                      const float* in_shift, const float* w, const float* bias, int Cout, int relu, void* d_out) {
-  if (!d_in_nchw || !w || !d_out || dtype < 1 || dtype > 2) { g_error = "b200rn_stem_conv: bad argument"; return B200RN_ERR_ARG; }
+  if (!d_in_nchw || !w || !d_out || dtype < 0 || dtype > 2) { g_error = "b200rn_stem_conv: bad argument"; return B200RN_ERR_ARG; }
   return guarded(nullptr, [&] {
     DType dt = DType(dtype);
     const int Hp = stem_Hp(H), Wp = stem_Wp(W);
     const int Ho = (H + 6 - 7) / 2 + 1, Wo = (W + 6 - 7) / 2 + 1;
     ConvGeom g{B, H, W, 4, Ho, Wo, Cout, 7, 7, 2, 3};
+    if (dt == DType::F32) {
+      // exact mode: zero-framed fp32 input, 3 x TF32 stem (conv_tf32x3_kernel through its 5-D overlapping view)
+      if (!tf32_stem_supported(g)) throw ArgFail{"b200rn_stem_conv (fp32): needs an even image height and Cout % 64 == 0"};
+      std::vector<float> s4(4, 0.f), t4(4, 0.f), hb(size_t(Cout), 0.f);
+      for (int c = 0; c < 3; ++c) { s4[size_t(c)] = in_scale ? in_scale[c] : 1.f; t4[size_t(c)] = in_shift ? in_shift[c] : 0.f; }
+      if (bias) hb.assign(bias, bias + Cout);
+      std::vector<float> packed(tf32_stem_weight_elems(Cout)), hi(packed.size()), lo(packed.size());
+      tf32_pack_stem_weights(w, Cout, packed.data());
+      tf32_split_weights(packed.data(), packed.size(), hi.data(), lo.data());
+      struct Bufs {
+        void* p[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+        ~Bufs() { for (void* q : p) cudaFree(q); }
+      } bufs;
+      bufs.p[0] = upload(s4); bufs.p[1] = upload(t4); bufs.p[2] = upload(hb); bufs.p[3] = upload(hi); bufs.p[4] = upload(lo);
+      const size_t fbytes = size_t(B) * Hp * Wp * 4 * 4;
+      CK(cudaMalloc(&bufs.p[5], fbytes));
+      CK(cudaMemset(bufs.p[5], 0, fbytes));
+      CK(launch_input_xform(d_in_nchw, bufs.p[5], dt, B, 3, H, W, 4, Hp, Wp, 3, 3, static_cast<float*>(bufs.p[0]), static_cast<float*>(bufs.p[1]), 0, 0));
+      Epilogue e;
+      e.bias = static_cast<float*>(bufs.p[2]); e.relu = relu; e.out = d_out;
+      char msg[512] = {0};
+      Tf32ConvPlan* tp = tf32_conv_plan_create(g, static_cast<const float*>(bufs.p[5]), static_cast<float*>(bufs.p[3]), static_cast<float*>(bufs.p[4]), e,
+                                               msg, sizeof msg, 1);
+      if (!tp) throw CudaFail{std::string("b200rn_stem_conv: ") + msg};
+      cudaError_t le = launch_conv_tf32(tp, 0);
+      cudaError_t se = cudaDeviceSynchronize();
+      tf32_conv_plan_destroy(tp);
+      unsigned int flag = 0;
+      if (se == cudaSuccess) se = umma_take_timeout_flag(&flag);
+      if (le != cudaSuccess || se != cudaSuccess || flag)
+        throw CudaFail{fmt("b200rn_stem_conv (fp32): launch %s / sync %s / barrier timeout %u", cudaGetErrorString(le), cudaGetErrorString(se), flag)};
+      return;
+    }
     std::vector<float> s4(4, 0.f), t4(4, 0.f);
     for (int c = 0; c < 3; ++c) { s4[size_t(c)] = in_scale ? in_scale[c] : 1.f; t4[size_t(c)] = in_shift ? in_shift[c] : 0.f; }
     float* ds = upload(s4); float* dsh = upload(t4);

@@ -25,8 +25,10 @@ extern "C" {
 typedef struct b200rn b200rn_t;
 
 /* Arithmetic modes.
- *  EXACT: fp32 storage and fp32 FMA accumulation on CUDA cores; logits within 1e-3 max-abs of the
- *         fp32 CPU oracle (the north-star's "fp32 accumulate" bar).
+ *  EXACT: fp32 storage; convolutions as 3 x TF32 split products on the tensor cores with two-level fp32
+ *         accumulation (chunks in tensor memory, chunk sums in registers), FC on CUDA cores; logits within 1e-3
+ *         max-abs of the fp32 CPU oracle (the north-star's "fp32 accumulate" bar).  B200RN_EXACT_SIMT=1 in the
+ *         environment keeps every convolution on the fp32 CUDA-core kernel instead.
  *  BF16 / FP16: 16-bit NHWC activations and weights, tcgen05 tensor cores, fp32 accumulation in
  *         TMEM; judged by top-1 agreement. */
 enum { B200RN_MODE_EXACT = 0, B200RN_MODE_BF16 = 1, B200RN_MODE_FP16 = 2 };
@@ -121,7 +123,8 @@ int b200rn_time_forward(b200rn_t* h, const float* const* d_inputs, int n_inputs,
 
 /* ---- single-operator entry point (tests of the conv kernels against a framework reference) ----
  * NHWC convolution with the fused epilogue, device pointers, on the current device.
- * dtype: 0 fp32 (CUDA-core path), 1 bf16, 2 fp16 (tcgen05 path).  w: fp32 host weights
+ * dtype: 0 fp32 (exact mode: 3 x TF32 on tcgen05 where Cin % 32 == 0 and Cout % 64 == 0, else -- or with
+ * B200RN_EXACT_SIMT=1 -- the CUDA-core kernel), 1 bf16, 2 fp16 (tcgen05 path).  w: fp32 host weights
  * [Cout][kh][kw][Cin]; bias/act_scale/act_shift: fp32 host arrays [Cout] (act_* may be NULL).
  * residual / out / out_act are device NHWC tensors of dtype (any of them may be NULL except that
  * one output must exist).  pre_scale / pre_shift (fp32 host arrays [Cin], may be NULL; 1x1 pad-0 convs
@@ -149,7 +152,8 @@ int b200rn_conv1x1_two_input(int dtype, const void* d_in, int B, int H, int W, i
                              int Cin_b, int stride_b, const float* w, const float* bias, int Cout, void* d_out,
                              void* d_out_act, const float* act_scale, const float* act_shift, int act_relu);
 /* Same, for the 7x7/2 stem through the tensor-core path: d_in_nchw is fp32 NCHW [B,3,H,W]; the
- * input re-layout (with per-channel scale/shift) and the conv run back to back. */
+ * input re-layout (with per-channel scale/shift) and the conv run back to back.  dtype 0 (fp32 output, even H) is the
+ * exact-mode form: zero-framed fp32 input, 3 x TF32 split products with two-level accumulation. */
 int b200rn_stem_conv(int dtype, const float* d_in_nchw, int B, int H, int W, const float* in_scale,
                      const float* in_shift, const float* w, const float* bias, int Cout, int relu, void* d_out);
 

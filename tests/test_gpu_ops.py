@@ -51,7 +51,7 @@ def test_conv2d_large_k_without_cta_pairs(dtype, name, kw, monkeypatch):
     assert r["out"]["viol"] == 0, (name, r["out"])
 
 
-@pytest.mark.parametrize("dtype", [1, 2], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("dtype", [0, 1, 2], ids=["fp32", "bf16", "fp16"])
 @pytest.mark.parametrize("shape", [(2, 224, 224), (3, 64, 64), (1, 32, 32)])
 def test_stem_conv(dtype, shape):
     r = gh.stem_case(dtype, *shape)
