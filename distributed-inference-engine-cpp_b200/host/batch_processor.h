@@ -72,8 +72,11 @@ class BatchProcessor {
       p.promise.set_exception(std::make_exception_ptr(std::runtime_error("BatchProcessor stopped")));
   }
 
-  Response process(const Request& request) {
-    Pending p{request, std::promise<Response>()};
+  Response process(const Request& request) { return process(Request(request)); }
+
+  // the request is moved into the queue (no copy of its payload)
+  Response process(Request&& request) {
+    Pending p{std::move(request), std::promise<Response>()};
     std::future<Response> fut = p.promise.get_future();
     {
       std::lock_guard<std::mutex> g(mu_);

@@ -243,8 +243,14 @@ bool Server::serve_one(Conn* c) {
       if (k <= 0) return false;
       buf.append(tmp, size_t(k));
     }
-    req.body.assign(buf, body_at, need);
-    buf.erase(0, body_at + need);
+    // the body is handed over without a second buffer: the connection's buffer becomes the request's body (bytes of a
+    // pipelined next request, rare, are kept aside) and its storage goes back to the connection after the handler
+    std::string rest;
+    if (buf.size() > body_at + need) rest.assign(buf, body_at + need, std::string::npos);
+    buf.resize(body_at + need);
+    buf.erase(0, body_at);
+    req.body.swap(buf);
+    buf = std::move(rest);
 
     Response res;
     auto it = routes_.find(req.method + " " + req.path);
@@ -269,6 +275,10 @@ bool Server::serve_one(Conn* c) {
     std::string head = "HTTP/1.1 " + std::to_string(res.status) + " " + reason(res.status) + "\r\nContent-Type: " + res.content_type +
                        "\r\nContent-Length: " + std::to_string(res.body.size()) + "\r\nConnection: " +
                        (close_conn ? "close" : "keep-alive") + "\r\n\r\n";
+    if (buf.empty()) {                       // keep the large allocation with the connection for its next request
+      req.body.clear();
+      buf.swap(req.body);
+    }
     if (!send_all(fd, head.data(), head.size()) || !send_all(fd, res.body.data(), res.body.size())) return false;
     return !close_conn;
   }

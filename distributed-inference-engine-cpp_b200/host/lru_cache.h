@@ -53,7 +53,10 @@ class LRUCache {
     return it->second->value;
   }
 
-  void put(const Key& key, const Value& value) {
+  void put(const Key& key, const Value& value) { put(Key(key), value); }
+
+  // the key is moved into the entry (the caller's copy of a 602 KB sample is the one the cache keeps)
+  void put(Key&& key, const Value& value) {
     std::lock_guard<std::mutex> g(mu_);
     auto it = index_.find(&key);
     if (it != index_.end()) {
@@ -68,7 +71,7 @@ class LRUCache {
       delete victim;
       --count_;
     }
-    Item* item = new Item{key, value, nullptr, nullptr};
+    Item* item = new Item{std::move(key), value, nullptr, nullptr};
     index_.emplace(&item->key, item);
     pushNewest(item);
     ++count_;

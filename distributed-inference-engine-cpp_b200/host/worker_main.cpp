@@ -71,9 +71,9 @@ int main(int argc, char** argv) {
         auto id = req.headers.find("x-request-id");
         if (id == req.headers.end()) throw std::runtime_error("octet-stream request without an X-Request-Id header");
         if (req.body.size() % sizeof(float)) throw std::runtime_error("octet-stream body is not a whole number of float32 values");
-        std::vector<float> data(req.body.size() / sizeof(float));
-        std::memcpy(data.data(), req.body.data(), req.body.size());
-        res.set_content(worker.handleInferRaw(id->second, data).dump(), "application/json");
+        const float* first = reinterpret_cast<const float*>(req.body.data());
+        std::vector<float> data(first, first + req.body.size() / sizeof(float));
+        res.set_content(worker.handleInferRaw(id->second, std::move(data)).dump(), "application/json");
         return;
       }
       if (fast) res.set_content(worker.handleInferBody(req.body).dump(), "application/json");

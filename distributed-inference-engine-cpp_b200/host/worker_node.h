@@ -62,15 +62,15 @@ class WorkerNodeT {
     std::vector<float> input_data;
     if (fast_request::parse(body, request_id, input_data)) {
       ++total_requests_;
-      return handleInferFields(request_id, input_data);
+      return handleInferFields(request_id, std::move(input_data));
     }
     return handleInfer(json::parse(body));
   }
 
   // Entry for requests whose fields arrive already decoded (the octet-stream side channel).
-  json handleInferRaw(const std::string& request_id, const std::vector<float>& input_data) {
+  json handleInferRaw(const std::string& request_id, std::vector<float> input_data) {
     ++total_requests_;
-    return handleInferFields(request_id, input_data);
+    return handleInferFields(request_id, std::move(input_data));
   }
 
   json handleInfer(const json& request) {
@@ -85,12 +85,14 @@ class WorkerNodeT {
     };
     std::string request_id = field("request_id");
     std::vector<float> input_data = field("input_data");
-    return handleInferFields(request_id, input_data);
+    return handleInferFields(request_id, std::move(input_data));
   }
 
   // The handler after its two fields have been read (by the conversions above, or by fast_request::parse from the
-  // raw body); the caller has counted the request.
-  json handleInferFields(const std::string& request_id, const std::vector<float>& input_data) {
+  // raw body); the caller has counted the request.  The sample is taken by value: on a miss it is MOVED into the batch
+  // (the reference copies it into the request and again into the queue, src/worker_node.cpp:71, batch_processor.h:98)
+  // after one copy has been kept as the cache key.
+  json handleInferFields(const std::string& request_id, std::vector<float> input_data) {
     if (auto hit = cache_.get(input_data)) {
       ++cache_hits_;
       json response;
@@ -101,9 +103,9 @@ class WorkerNodeT {
       response["inference_time_us"] = 50;
       return response;
     }
-    InferenceRequest req{request_id, input_data};
-    InferenceResponse resp = batcher_.process(req);
-    cache_.put(input_data, resp.output_data);
+    std::vector<float> key(input_data);                       // the cache stores its key; everything else moves
+    InferenceResponse resp = batcher_.process(InferenceRequest{request_id, std::move(input_data)});
+    cache_.put(std::move(key), resp.output_data);
 
     json response;
     response["request_id"] = resp.request_id;

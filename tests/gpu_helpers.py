@@ -261,3 +261,18 @@ CONV_CASES = [
     # large-K plain 1x1 conv with at least two waves of tiles: the wide kernel's four-stage configuration
     ("deep 512->256 @28 B50 (306 tiles)", dict(B=50, H=28, W=28, Cin=512, Cout=256, k=1, stride=1, pad=0, relu=1)),
 ]
+
+
+# exact mode only (fp32 storage, 3 x TF32 on the tensor cores): channel counts the 16-bit kernels do not take (32-multiples),
+# the 64-wide N tile with one chunk per epilogue group, K that is not a whole number of 4-block accumulation chunks,
+# residual + both outputs on a ragged patch, a strided 3x3, and a shape the tensor-core form refuses (falls back to CUDA cores)
+FP32_CASES = [
+    ("t32 1x1 96->64 @28 B3 (3 K blocks)", dict(B=3, H=28, W=28, Cin=96, Cout=64, k=1, stride=1, pad=0, relu=1)),
+    ("t32 3x3 32->192 @14 B5 (9 K blocks, N=64 x3)", dict(B=5, H=14, W=14, Cin=32, Cout=192, k=3, stride=1, pad=1, relu=1)),
+    ("t32 1x1 160->128 @13x9 B2 res raw+act", dict(B=2, H=13, W=9, Cin=160, Cout=128, k=1, stride=1, pad=0, residual=True,
+                                                   want_out=True, want_act=True)),
+    ("t32 3x3 s2 96->128 @30x17 B3 act-only", dict(B=3, H=30, W=17, Cin=96, Cout=128, k=3, stride=2, pad=1, relu=1,
+                                                   want_out=False, want_act=True)),
+    ("t32 1x1 2048->64 @7 B40 (64 K blocks, 16 chunks)", dict(B=40, H=7, W=7, Cin=2048, Cout=64, k=1, stride=1, pad=0)),
+    ("fallback 1x1 48->40 @14 B2 (CUDA cores)", dict(B=2, H=14, W=14, Cin=48, Cout=40, k=1, stride=1, pad=0, relu=1)),
+]

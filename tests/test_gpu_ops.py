@@ -23,6 +23,15 @@ def test_conv2d(dtype, name, kw, monkeypatch):
             assert r[key]["viol"] == 0, (name, key, r[key])
 
 
+@pytest.mark.parametrize("name,kw", gh.FP32_CASES, ids=[c[0] for c in gh.FP32_CASES])
+def test_conv2d_exact_mode_shapes(name, kw):
+    r = gh.conv_case(0, **kw)
+    assert r["rc"] == 0, r["msg"]
+    for key in ("out", "act"):
+        if key in r:
+            assert r[key]["viol"] == 0, (name, key, r[key])
+
+
 SIMT_CASES = [c for c in gh.CONV_CASES if c[0] in ("1x1 s1 64->64 @56 B2", "3x3 s1 128->128 @28 B5", "1x1 s2 256->512 @56 B2",
                                                    "1x1 64->256 @14 res+dual", "3x3 s2 512->512 @14 B33")]
 

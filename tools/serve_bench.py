@@ -61,6 +61,8 @@ def main():
     ap.add_argument("--mode", default="fp16")
     ap.add_argument("--workers", type=int, default=1)
     ap.add_argument("--gateway", action="store_true")
+    ap.add_argument("--native", action="store_true",
+                    help="drive the load with the C++ generator (distributed-inference-engine-cpp_b200/loadgen) instead of Python threads")
     a = ap.parse_args()
     a_workers = max(1, a.workers)
     import torch
@@ -105,6 +107,25 @@ def main():
                 w = np.full(150528, 1000.0 + k, dtype=np.float32)
                 requests.post("http://" + ad + "/infer", data=json.dumps({"request_id": "warm_%d" % k, "input_data": w.tolist()}),
                               timeout=120)
+        if a.native:
+            host, port = url[len("http://"):].split(":")
+            lg = os.path.join(b200rn_loader.PKG_DIR, "loadgen")
+
+            def native(kind, n):
+                r = subprocess.run([lg, host, port, str(a.threads), str(n), kind], stdout=subprocess.PIPE, text=True, timeout=900)
+                return json.loads(r.stdout.strip().splitlines()[-1])
+
+            out = {"client": "native (host/loadgen_main.cpp), one keep-alive connection per thread",
+                   "cache_path_3_floats": native("small", a.requests * 16),
+                   "inference_path_150528_floats": native("json", a.requests),
+                   "inference_path_octet_stream": native("octet", a.requests * 4)}
+            out["config"] = {"workers": a_workers, "gpus": ngpu, "gateway": bool(a.gateway), "threads": a.threads, "mode": a.mode,
+                             "inflight": os.environ.get("B200RN_INFLIGHT", "1"), "fill_wait": os.environ.get("B200RN_FILL_WAIT", "0")}
+            out["health"] = [requests.get("http://" + ad + "/health", timeout=5).json() for ad in addrs]
+            if a.gateway:
+                out["stats"] = requests.get(url + "/stats", timeout=5).json()
+            print(json.dumps(out))
+            return
         small = [json.dumps({"request_id": "req_%d" % i, "input_data": [float(i % 10), float(i % 10 + 1), float(i % 10 + 2)]})
                  for i in range(a.requests * 4)]
         out = {"cache_path_3_floats": run(url, small, a.threads)}
