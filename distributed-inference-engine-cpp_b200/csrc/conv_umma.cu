@@ -95,6 +95,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       "}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
   return ok != 0;
 }
+// non-blocking probe (mbarrier.test_wait never suspends the thread): used to look ahead at a barrier that is normally
+// complete already without stalling on it when it is not
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, P1;\n\t"
+      "}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
@@ -649,7 +661,7 @@ struct HaloParams {
   int cblks, n_tiles, total_tiles, tiles_w, tiles_h;
   int halo_stages, b_stages, b_stationary, relu;
   unsigned long long* trace;   // timeline experiment (B200RN_DBG_TRACE): CTA 0 stamps clock64 per tile and actor
-  int dbg_skip;   // bottleneck experiment (B200RN_DBG_SKIP): 1 = issue no MMA, 2 = no epilogue math/stores, 4 = one MMA per tap
+  int dbg_skip;   // bottleneck experiment (B200RN_DBG_SKIP): 1 = issue no MMA, 2 = no epilogue math/stores, 4 = one MMA per tap, 8 = taps ignore their kx row shift (atom-aligned descriptors; wrong results)
   const float* bias;
 };
 
@@ -763,51 +775,68 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmHalo, const __grid_con
       const uint32_t halo_lo = smem_desc_lo(smem_u32(halo));
       const uint32_t bbuf_lo = smem_desc_lo(smem_u32(bbuf));
       if (p.b_stationary && my_tiles > 0) mbar_wait(smem_u32(&b_full[0]), 0);
-      int q = 0, bstage = 0;
-      uint32_t bphase = 0;
-      for (int i = 0; i < my_tiles; ++i) {
+      // The issuing thread must not leave the tensor core without queued work between tiles: a tile here is only 36
+      // short MMAs (~1600 cycles), and the timeline (B200RN_DBG_TRACE) showed ~900 cycles per tile spent in this thread
+      // on barrier polls (~90 cycles each even when already complete), commits and ring arithmetic with nothing issued.
+      // So the NEXT unit's barriers (its patch; for a new tile also its accumulator) are probed before the last two
+      // taps of the current unit are issued, while earlier taps are still queued -- without blocking: a blocking
+      // look-ahead cost the dual-M form 12 % when the next patch had not landed yet -- and the ring position is kept
+      // incrementally (no division by the runtime stage count).
+      const int units = my_tiles * p.cblks;
+      int bstage = 0, slot = 0, i = 0, cb = 0;
+      uint32_t bphase = 0, hphase = 0;
+      bool ready = false;                        // this unit's barriers were already seen complete by the look-ahead
+      for (int q = 0; q < units; ++q) {
         const int buf = i & 1;
-        if (p.trace && blockIdx.x == 0 && i < 64) p.trace[i * 8 + 6] = clock64();
-        mbar_wait(smem_u32(&tmem_empty[buf]), ((i >> 1) & 1) ^ 1);
-        tc_fence_after();
-        if (p.trace && blockIdx.x == 0 && i < 64) p.trace[i * 8 + 7] = clock64();
-        const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
-        for (int cb = 0; cb < p.cblks; ++cb, ++q) {
-          const int slot = q % HS;
-          if (p.trace && blockIdx.x == 0 && q < 64) p.trace[q * 8 + 1] = clock64();
-          mbar_wait(smem_u32(&halo_full[slot]), uint32_t(q / HS) & 1);
-          tc_fence_after();
-          if (p.trace && blockIdx.x == 0 && q < 64) p.trace[q * 8 + 2] = clock64();
-          const uint32_t a_lo = halo_lo + uint32_t(slot) * (kHaloStageBytes >> 4);
-#pragma unroll
-          for (int tap = 0; tap < 9; ++tap) {
-            uint32_t b_lo;
-            if (p.b_stationary) {
-              b_lo = bbuf_lo + uint32_t(tap * p.cblks + cb) * (B_BYTES >> 4);
-            } else {
-              mbar_wait(smem_u32(&b_full[bstage]), bphase);
-              tc_fence_after();
-              b_lo = bbuf_lo + uint32_t(bstage) * (B_BYTES >> 4);
-            }
-            // row-shifted view of the patch: tap (ky,kx) starts ky*16 + kx rows (of 128 bytes) further on
-            const uint32_t a_tap = a_lo + uint32_t((tap / 3) * kHaloPW + (tap % 3)) * 8;
-            if (!(p.dbg_skip & 1)) {
-#pragma unroll
-              for (int k = 0; k < 4; ++k)
-                if (k == 0 || !(p.dbg_skip & 4))
-                  umma_f16_lo(tmem_d, a_tap + 2 * k, b_lo + 2 * k, desc_hi, idesc, (tap | k) != 0 ? 1u : uint32_t(cb != 0));
-            }
-            if (!p.b_stationary) {
-              umma_commit(smem_u32(&b_empty[bstage]));
-              if (++bstage == SB) { bstage = 0; bphase ^= 1; }
-            }
-          }
-          if (p.trace && blockIdx.x == 0 && q < 64) p.trace[q * 8 + 3] = clock64();
-          umma_commit(smem_u32(&halo_empty[slot]));
-          if (p.trace && blockIdx.x == 0 && q < 64) p.trace[q * 8 + 4] = clock64();
-          if (cb == p.cblks - 1) umma_commit(smem_u32(&tmem_full[buf]));
-          if (p.trace && blockIdx.x == 0 && q < 64) p.trace[q * 8 + 5] = clock64();
+        const bool tr = p.trace && blockIdx.x == 0 && q < 64;
+        if (!ready) {
+          if (cb == 0) mbar_wait(smem_u32(&tmem_empty[buf]), ((uint32_t(i) >> 1) & 1) ^ 1);
+          mbar_wait(smem_u32(&halo_full[slot]), hphase);
         }
+        tc_fence_after();
+        if (tr) p.trace[q * 8 + 2] = clock64();
+        const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
+        const uint32_t a_lo = halo_lo + uint32_t(slot) * (kHaloStageBytes >> 4);
+        const bool last_cb = cb == p.cblks - 1;
+        int nslot = slot + 1;
+        uint32_t nphase = hphase;
+        if (nslot == HS) { nslot = 0; nphase ^= 1; }
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+          if (tap == 7) {                       // look ahead (non-blocking: if not complete yet, the top of the next unit waits)
+            if (tr) p.trace[q * 8 + 1] = clock64();
+            ready = q + 1 < units && mbar_test(smem_u32(&halo_full[nslot]), nphase) &&
+                    (!last_cb || mbar_test(smem_u32(&tmem_empty[(i + 1) & 1]), ((uint32_t(i + 1) >> 1) & 1) ^ 1));
+            if (tr) p.trace[q * 8 + 7] = clock64();
+          }
+          uint32_t b_lo;
+          if (p.b_stationary) {
+            b_lo = bbuf_lo + uint32_t(tap * p.cblks + cb) * (B_BYTES >> 4);
+          } else {
+            mbar_wait(smem_u32(&b_full[bstage]), bphase);
+            tc_fence_after();
+            b_lo = bbuf_lo + uint32_t(bstage) * (B_BYTES >> 4);
+          }
+          // row-shifted view of the patch: tap (ky,kx) starts ky*16 + kx rows (of 128 bytes) further on
+          const uint32_t a_tap = a_lo + uint32_t((tap / 3) * kHaloPW + ((p.dbg_skip & 8) ? 0 : (tap % 3))) * 8;   // dbg 8: no kx shift (timing only)
+          if (!(p.dbg_skip & 1)) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              if (k == 0 || !(p.dbg_skip & 4))
+                umma_f16_lo(tmem_d, a_tap + 2 * k, b_lo + 2 * k, desc_hi, idesc, (tap | k) != 0 ? 1u : uint32_t(cb != 0));
+          }
+          if (!p.b_stationary) {
+            umma_commit(smem_u32(&b_empty[bstage]));
+            if (++bstage == SB) { bstage = 0; bphase ^= 1; }
+          }
+        }
+        if (tr) p.trace[q * 8 + 3] = clock64();
+        umma_commit(smem_u32(&halo_empty[slot]));
+        if (tr) p.trace[q * 8 + 4] = clock64();
+        if (last_cb) umma_commit(smem_u32(&tmem_full[buf]));
+        if (tr) p.trace[q * 8 + 5] = clock64();
+        slot = nslot; hphase = nphase;
+        if (last_cb) { cb = 0; ++i; } else ++cb;
       }
     }
   } else {
@@ -1034,26 +1063,39 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
     if (elect_one() && my_tiles > 0) {
       mbar_wait(smem_u32(w_bar), 0);
       const uint32_t w_addr = smem_u32(wbuf);
-      int stage = 0;
-      uint32_t phase = 0;
+      // A tile is 14 short MMAs: the next tile's barriers (patch landed, accumulator drained) are probed before the last
+      // four are issued, while the earlier ones are still queued, so the tensor core is not left idle over the polls
+      // (~90 cycles each even when complete) and commits between tiles; ring and accumulator indices are kept incrementally.
+      int stage = 0, buf = 0;
+      uint32_t phase = 0, eround = 0;           // eround = i / G
+      bool ready = false;
       for (int i = 0; i < my_tiles; ++i) {
-        const int buf = i % G;
-        mbar_wait(smem_u32(&tmem_empty[buf]), (uint32_t(i / G) & 1) ^ 1);
-        mbar_wait(smem_u32(&full_bar[stage]), phase);
+        if (!ready) {
+          mbar_wait(smem_u32(&tmem_empty[buf]), (eround & 1) ^ 1);
+          mbar_wait(smem_u32(&full_bar[stage]), phase);
+        }
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
         const uint32_t a_addr = smem_u32(patch + stage * kStemStageBytes);
+        int nstage = stage + 1, nbuf = buf + 1;
+        uint32_t nphase = phase, nround = eround;
+        if (nstage == S) { nstage = 0; nphase ^= 1; }
+        if (nbuf == G) { nbuf = 0; ++nround; }
 #pragma unroll
-        for (int ky = 0; ky < 7; ++ky)
+        for (int ky = 0; ky < 7; ++ky) {
+          if (ky == 5)                          // look ahead, non-blocking
+            ready = i + 1 < my_tiles && mbar_test(smem_u32(&full_bar[nstage]), nphase) &&
+                    mbar_test(smem_u32(&tmem_empty[nbuf]), (nround & 1) ^ 1);
 #pragma unroll
           for (int m = 0; m < 2; ++m) {
             const uint64_t da = make_desc_noswz(a_addr + ky * kStemPatchPitch + m * 32, 16, 2 * kStemPatchPitch);
             const uint64_t db = make_desc_noswz(w_addr + ky * 4096 + m * 256, 128, 512);
             umma_f16(tmem_d, da, db, idesc, (ky | m) != 0 ? 1u : 0u);
           }
+        }
         umma_commit(smem_u32(&empty_bar[stage]));
         umma_commit(smem_u32(&tmem_full[buf]));
-        if (++stage == S) { stage = 0; phase ^= 1; }
+        stage = nstage; phase = nphase; buf = nbuf; eround = nround;
       }
     }
   } else {
@@ -1350,6 +1392,7 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
 }
 
+#include "conv_halo2.cuh"
 #include "conv_tail.cuh"
 #include "conv_wide.cuh"
 #include "conv_pair.cuh"
@@ -1424,6 +1467,8 @@ struct UmmaConvPlan {
   int grid;
   int halo = 0;           // 3x3/s1/p1 layer routed to conv3x3_halo_kernel (tmA = patch map, tmOut = row-store map)
   HaloParams hp;
+  int halo2 = 0;          // ... to conv3x3_halo2_kernel (two M tiles per streamed weight tile) when the slab does not fit
+  Halo2Params h2;
   int dual = 0;           // large-K layer routed to conv_dualm_kernel (two M tiles per weight tile)
   DualParams dp;
   int pair = 0;           // large-K layer routed to conv_pair_kernel (CTA pair, tcgen05.mma.cta_group::2, M = 256)
@@ -1698,6 +1743,20 @@ static cudaError_t launch_halo(const UmmaConvPlan* pl, cudaStream_t s) {
   return launch_pdl(kern, pl->grid, kTwoGroupThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmOut, pl->hp);
 }
 
+template <typename T, int BLOCK_N>
+static cudaError_t launch_halo2(const UmmaConvPlan* pl, cudaStream_t s) {
+  auto kern = conv3x3_halo2_kernel<T, BLOCK_N>;
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    configured_device = dev;
+  }
+  return launch_pdl(kern, pl->grid, kTwoGroupThreads, pl->smem_bytes, s, pl->tmA, pl->tmW, pl->tmOut, pl->h2);
+}
+
 template <typename T>
 static cudaError_t launch_stem2(const UmmaConvPlan* pl, cudaStream_t s) {
   auto kern = stem7x7_kernel<T>;
@@ -1797,6 +1856,10 @@ cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
     return bf ? launch_dual<__nv_bfloat16, 256>(pl, s) : launch_dual<__half, 256>(pl, s);
   }
   if (pl->stem2) return bf ? launch_stem2<__nv_bfloat16>(pl, s) : launch_stem2<__half>(pl, s);
+  if (pl->halo2) {
+    if (pl->block_n == 64) return bf ? launch_halo2<__nv_bfloat16, 64>(pl, s) : launch_halo2<__half, 64>(pl, s);
+    return bf ? launch_halo2<__nv_bfloat16, 128>(pl, s) : launch_halo2<__half, 128>(pl, s);
+  }
   if (pl->halo) {
     if (pl->block_n == 64) return bf ? launch_halo<__nv_bfloat16, 64>(pl, s) : launch_halo<__half, 64>(pl, s);
     return bf ? launch_halo<__nv_bfloat16, 128>(pl, s) : launch_halo<__half, 128>(pl, s);
@@ -2007,6 +2070,25 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       hp.halo_stages = std::max(2, std::min(8, int((budget - fixed) / kHaloStageBytes)));
       pl->smem_bytes = fixed + uint32_t(hp.halo_stages) * kHaloStageBytes;
       pl->grid = grid;
+      {
+        // The weight slab does not fit (it is streamed per tile): two M tiles per streamed weight tile instead
+        // (conv3x3_halo2_kernel).  Measured with the MMAs switched off these layers ran at the pace of that stream.
+        const char* h2env = std::getenv("B200RN_HALO2");
+        const int m_tiles = hp.tiles_w * hp.tiles_h * g.B;
+        if (!(h2env && h2env[0] == '0') && !hp.b_stationary && m_tiles >= 2 && !hp.trace && !hp.dbg_skip) {
+          Halo2Params& h2 = pl->h2;
+          std::memset(&h2, 0, sizeof h2);
+          pl->halo2 = 1;
+          h2.cblks = hp.cblks; h2.n_tiles = hp.n_tiles; h2.m_tiles = m_tiles; h2.tiles_w = hp.tiles_w; h2.tiles_h = hp.tiles_h;
+          h2.total_items = ((m_tiles + 1) / 2) * hp.n_tiles;
+          h2.relu = hp.relu; h2.bias = hp.bias;
+          h2.b_stages = 4;
+          const uint32_t fixed2 = 1024u + 4u * b_bytes + 2 * out_bytes + 2u * uint32_t(pl->block_n) * 4 + 8u * (2 * 8 + 2 * 4 + 4) + 64;
+          h2.halo_stages = std::max(2, std::min(6, int((budget - fixed2) / (2 * kHaloStageBytes))));
+          pl->smem_bytes = fixed2 + uint32_t(h2.halo_stages) * 2 * kHaloStageBytes;
+          pl->grid = std::min(h2.total_items, sms);
+        }
+      }
       std::string hmsg;
       uint64_t dims[4] = {uint64_t(g.Cin), uint64_t(g.W), uint64_t(g.H), uint64_t(g.B)};
       uint64_t str[3] = {uint64_t(g.Cin) * 2, uint64_t(g.W) * g.Cin * 2, uint64_t(g.H) * g.W * g.Cin * 2};
@@ -2312,7 +2394,7 @@ void umma_conv_plan_destroy(UmmaConvPlan* p) {
     cudaDeviceSynchronize();
     cudaMemcpy(h.data(), p->hp.trace, h.size() * 8, cudaMemcpyDeviceToHost);
     unsigned long long t0 = h[0];
-    std::fprintf(stderr, "tile: load_issue | mma_wait_begin mma_got_halo mma_issued after_commit1 after_commit2 | tile_top after_tmem_empty (cycles)\n");
+    std::fprintf(stderr, "unit: load_issue | lookahead_wait_begin unit_top mma_issued after_commit1 after_commit2 | - lookahead_wait_end (cycles)\n");
     for (int i = 0; i < 24; ++i) {
       std::fprintf(stderr, "%2d:", i);
       for (int k = 0; k < 8; ++k) std::fprintf(stderr, " %8lld", h[i * 8 + k] ? (long long)(h[i * 8 + k] - t0) : -1LL);

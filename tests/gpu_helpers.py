@@ -249,6 +249,10 @@ CONV_CASES = [
                                                            residual=True, want_out=True, want_act=True)),
     ("wide s2 512->1024 @28 B9 shortcut", dict(B=9, H=28, W=28, Cin=512, Cout=1024, k=1, stride=2, pad=0)),
     ("wide 64->256 @13x9 B3 ragged res raw", dict(B=3, H=13, W=9, Cin=64, Cout=256, k=1, stride=1, pad=0, residual=True)),
+    # dual-M halo kernel (weight slab streamed: two M tiles per weight tile): an odd number of M tiles (the item's second
+    # tile lies outside the batch), more items than SMs x 2 (both accumulator pairs reused)
+    ("halo2 3x3 128->128 @24x14 B1 (3 M tiles)", dict(B=1, H=24, W=14, Cin=128, Cout=128, k=3, stride=1, pad=1, relu=1)),
+    ("halo2 3x3 128->128 @28 B80 (640 M tiles)", dict(B=80, H=28, W=28, Cin=128, Cout=128, k=3, stride=1, pad=1, relu=1)),
     # CTA-pair kernel (tcgen05.mma.cta_group::2, one 256 x N tile per 2-SM cluster): N = 128 halves, an odd number of
     # M tiles (the pair's second tile lies wholly outside the batch), one pair only, more items than clusters x 2
     # (both accumulators of the double buffer reused), strided 3x3 taps through the pair's TMA loads

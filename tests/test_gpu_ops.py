@@ -47,6 +47,19 @@ def test_conv2d_fp32_cuda_core_kernel(name, kw, monkeypatch):
             assert r[key]["viol"] == 0, (name, key, r[key])
 
 
+HALO_CASES = [c for c in gh.CONV_CASES if "halo" in c[0] or c[0] in ("3x3 s1 64->64 @56 B2", "3x3 s1 128->128 @28 B5")]
+
+
+@pytest.mark.parametrize("dtype", [1, 2], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("name,kw", HALO_CASES, ids=[c[0] for c in HALO_CASES])
+def test_conv3x3_single_m_halo_kernel(dtype, name, kw, monkeypatch):
+    """B200RN_HALO2=0: the one-M-tile halo kernel also where the weight slab is streamed (the dual-M form's predecessor)."""
+    monkeypatch.setenv("B200RN_HALO2", "0")
+    r = gh.conv_case(dtype, **kw)
+    assert r["rc"] == 0, r["msg"]
+    assert r["out"]["viol"] == 0, (name, r["out"])
+
+
 SINGLE_SM_CASES = [c for c in gh.CONV_CASES if "dual-M" in c[0] or c[0].startswith("pair")]
 
 
