@@ -18,3 +18,10 @@ for f in ("r2_bench_d", "r2_bench_exact_tf32", "r2_bench_exact_simt"):
         print(f, "ERR", e)
 PY
 tail -9 gpurun_out/r2_sweep.err
+# ncu launch list of one step (DRAM traffic stamp for bench.py's roofline.traffic)
+export B200RN_GRAPH=0
+CMD="python tools/profile_step.py --batch 256 --steps 1 --warmup 1"
+MET=gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed,sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active
+$CMD > gpurun_out/r2_ncu_plain.log 2>&1 && \
+ncu --metrics $MET --clock-control none -k regex:"conv|stem7x7|maxpool|gap_|input_xform" -s 51 -c 51 --csv --log-file gpurun_out/r2_launches.csv $CMD > gpurun_out/r2_ncu_list.log 2>&1
+tail -1 gpurun_out/r2_ncu_list.log
