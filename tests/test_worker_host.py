@@ -232,3 +232,21 @@ def test_idle_and_stalled_connections_do_not_hold_request_threads():
     finally:
         proc.terminate()
         proc.wait(timeout=5)
+
+
+def test_native_load_generator_against_the_worker(worker):
+    """host/loadgen_main.cpp (the closed-loop generator behind tools/serve_bench.py --native): every payload kind is
+    answered, the cache path hits after ten distinct keys, and the summary is well-formed JSON."""
+    lg = os.path.join(ROOT, "distributed-inference-engine-cpp_b200", "loadgen")
+    if not os.path.exists(lg):
+        pytest.skip("loadgen not built")
+    host, port = worker[len("http://"):].split(":")
+    before = requests.get(worker + "/health", timeout=2).json()
+    for kind, n, floats in (("small", 200, None), ("json", 24, 3000), ("octet", 24, 3000)):
+        cmd = [lg, host, port, "4", str(n), kind] + ([str(floats)] if floats else [])
+        out = subprocess.run(cmd, stdout=subprocess.PIPE, text=True, timeout=60).stdout
+        j = json.loads(out.strip().splitlines()[-1])
+        assert j["ok"] == n and j["failed"] == 0 and j["req_per_s"] > 0 and j["p50_ms"] <= j["p99_ms"], j
+    after = requests.get(worker + "/health", timeout=2).json()
+    assert after["total_requests"] - before["total_requests"] == 248
+    assert after["cache_hits"] - before["cache_hits"] >= 180          # 200 small requests over 10 distinct vectors
