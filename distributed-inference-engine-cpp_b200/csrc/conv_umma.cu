@@ -959,6 +959,9 @@ constexpr uint32_t kStemWBytes = 7 * 4096;                     // one 64-channel
 struct Stem2Params {
   int tiles_w, tiles_h, n_tiles, total_tiles, stages, relu;
   int groups;                // epilogue warp groups (8 warps each) working on consecutive tiles: 2, or 3 with the fused pool
+  int dbg_skip;              // timing experiments only (B200RN_STEM_DBG): 1 no MMAs, 2 no pool phase / store, 4 no TMEM read + staging,
+                             // 8 no patch loads, 16 no look-ahead
+  unsigned long long* trace; // timeline experiment (B200RN_DBG_TRACE): CTA 0 stamps clock64 per tile and actor
   const float* bias;
   const void* w_packed;
   // Fused 3x3 / stride-2 / pad-1 max-pool (pool != 0): a tile is still 8 x 16 conv outputs, but placed at conv
@@ -1032,13 +1035,30 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
   pdl_launch_dependents();
   pdl_wait_prior_grid();
 
-  auto tile_coord = [&](int i, int& x0, int& y0, int& n) {
-    int mt = (int(blockIdx.x) + i * int(gridDim.x)) / p.n_tiles;
-    const int tw = mt % p.tiles_w; mt /= p.tiles_w;
-    const int th = mt % p.tiles_h;
-    n = mt / p.tiles_h;
-    if (p.pool) { x0 = tw * 6 - 1; y0 = th * 14 - 1; }
-    else { x0 = tw * kStemTW; y0 = th * kStemTH; }
+  // Tile i of this CTA is M tile blockIdx.x / n_tiles + i * (gridDim.x / n_tiles), decomposed as (tw, th, image).  The
+  // decomposition is kept incrementally (five runtime divisions per tile cost the producer thread ~800 cycles, more than
+  // the tile's MMAs: timeline, B200RN_DBG_TRACE): `TileWalk` holds the coordinates of one tile and the per-step carry.
+  struct TileWalk {
+    int tw, th, n, sw, sh, sn, tiles_w, tiles_h;
+    __device__ __forceinline__ void init(int first, int step, int tiles_w_, int tiles_h_) {
+      tiles_w = tiles_w_; tiles_h = tiles_h_;
+      tw = first % tiles_w; first /= tiles_w; th = first % tiles_h; n = first / tiles_h;
+      sw = step % tiles_w; step /= tiles_w; sh = step % tiles_h; sn = step / tiles_h;
+    }
+    __device__ __forceinline__ void advance() {
+      tw += sw;
+      int c = 0;
+      if (tw >= tiles_w) { tw -= tiles_w; c = 1; }
+      th += sh + c;
+      c = 0;
+      if (th >= tiles_h) { th -= tiles_h; c = 1; }
+      n += sn + c;
+    }
+  };
+  const int walk_first = int(blockIdx.x) / p.n_tiles, walk_step = int(gridDim.x) / p.n_tiles;
+  auto tile_origin = [&](const TileWalk& t, int& x0, int& y0) {
+    if (p.pool) { x0 = t.tw * 6 - 1; y0 = t.th * 14 - 1; }
+    else { x0 = t.tw * kStemTW; y0 = t.th * kStemTH; }
   };
 
   if (warp == 0) {
@@ -1047,11 +1067,23 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
       bulk_load_1d(smem_u32(wbuf), static_cast<const uint8_t*>(p.w_packed) + size_t(n_tile) * kStemWBytes, kStemWBytes, smem_u32(w_bar));
       int stage = 0;
       uint32_t phase = 0;
-      for (int i = 0; i < my_tiles; ++i) {
-        int x0, y0, n;
-        tile_coord(i, x0, y0, n);
+      TileWalk t;
+      t.init(walk_first, walk_step, p.tiles_w, p.tiles_h);
+      for (int i = 0; i < my_tiles; ++i, t.advance()) {
+        int x0, y0;
+        tile_origin(t, x0, y0);
+        int n = t.n;
+        if (p.dbg_skip & 64) {                  // timing experiment: the five divisions the walk replaced
+          int mt = (int(blockIdx.x) + i * int(gridDim.x)) / p.n_tiles;
+          const int tw = mt % p.tiles_w; mt /= p.tiles_w;
+          const int th = mt % p.tiles_h;
+          n = mt / p.tiles_h;
+          x0 = p.pool ? tw * 6 - 1 : tw * kStemTW; y0 = p.pool ? th * 14 - 1 : th * kStemTH;
+        }
         mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
+        if (p.trace && blockIdx.x == 0 && i < 64) p.trace[i * 8 + 0] = clock64();
         const uint32_t fb = smem_u32(&full_bar[stage]);
+        if (p.dbg_skip & 8) { mbar_arrive(fb); if (++stage == S) { stage = 0; phase ^= 1; } continue; }
         mbar_expect_tx(fb, kStemPatchBytes);
         // frame coordinates: pixel (2*x0, 2*y0) of the zero-framed input = tap (0,0) of output (x0, y0)
         tma_load_3d(smem_u32(patch + stage * kStemStageBytes), &tmPatch, fb, 2 * x0 * 4, 2 * y0, n);
@@ -1070,11 +1102,14 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
       uint32_t phase = 0, eround = 0;           // eround = i / G
       bool ready = false;
       for (int i = 0; i < my_tiles; ++i) {
+        const bool tr = p.trace && blockIdx.x == 0 && i < 64;
+        if (tr) p.trace[i * 8 + 1] = clock64();
         if (!ready) {
           mbar_wait(smem_u32(&tmem_empty[buf]), (eround & 1) ^ 1);
           mbar_wait(smem_u32(&full_bar[stage]), phase);
         }
         tc_fence_after();
+        if (tr) p.trace[i * 8 + 2] = clock64();
         const uint32_t tmem_d = tmem_base + uint32_t(buf * BLOCK_N);
         const uint32_t a_addr = smem_u32(patch + stage * kStemStageBytes);
         int nstage = stage + 1, nbuf = buf + 1;
@@ -1084,17 +1119,21 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
 #pragma unroll
         for (int ky = 0; ky < 7; ++ky) {
           if (ky == 5)                          // look ahead, non-blocking
-            ready = i + 1 < my_tiles && mbar_test(smem_u32(&full_bar[nstage]), nphase) &&
+            ready = !(p.dbg_skip & 16) && i + 1 < my_tiles && mbar_test(smem_u32(&full_bar[nstage]), nphase) &&
                     mbar_test(smem_u32(&tmem_empty[nbuf]), (nround & 1) ^ 1);
 #pragma unroll
           for (int m = 0; m < 2; ++m) {
             const uint64_t da = make_desc_noswz(a_addr + ky * kStemPatchPitch + m * 32, 16, 2 * kStemPatchPitch);
             const uint64_t db = make_desc_noswz(w_addr + ky * 4096 + m * 256, 128, 512);
-            umma_f16(tmem_d, da, db, idesc, (ky | m) != 0 ? 1u : 0u);
+            if (!(p.dbg_skip & 1)) umma_f16(tmem_d, da, db, idesc, (ky | m) != 0 ? 1u : 0u);
           }
         }
-        umma_commit(smem_u32(&empty_bar[stage]));
+        if (tr) p.trace[i * 8 + 3] = clock64();
+        // one commit per tile (each costs this thread ~95 cycles): the epilogue group that sees the accumulator complete
+        // hands the patch slot back to the producer
+        if (p.dbg_skip & 32) umma_commit(smem_u32(&empty_bar[stage]));
         umma_commit(smem_u32(&tmem_full[buf]));
+        if (tr) p.trace[i * 8 + 4] = clock64();
         stage = nstage; phase = nphase; buf = nbuf; eround = nround;
       }
     }
@@ -1108,23 +1147,36 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
     const int sw = row & 7;
     const bool store_thread = (((warp - 2) & 7) == 0 && lane == 0);
     const int bar_id = 1 + grp;
-    for (int i = grp; i < my_tiles; i += G) {
-      int x0, y0, n;
-      tile_coord(i, x0, y0, n);
+    TileWalk t;
+    t.init(walk_first + grp * walk_step, G * walk_step, p.tiles_w, p.tiles_h);
+    int pstage = grp % S;                      // patch slot of tile i = i % S
+    uint32_t round = 0;                        // i / G
+    for (int i = grp; i < my_tiles; i += G, t.advance(), ++round) {
+      int x0, y0;
+      tile_origin(t, x0, y0);
+      const int n = t.n;
       const int buf = grp;
       if (store_thread && i > grp) tma_store_wait_read();   // this group's previous tile has left its staging buffer
+      const bool etr = p.trace && blockIdx.x == 0 && store_thread && i < 64;
+      if (etr) p.trace[i * 8 + 5] = clock64();
       asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
-      mbar_wait(smem_u32(&tmem_full[buf]), uint32_t(i / G) & 1);
+      mbar_wait(smem_u32(&tmem_full[buf]), round & 1);
       tc_fence_after();
+      if (store_thread && !(p.dbg_skip & 32)) mbar_arrive(smem_u32(&empty_bar[pstage]));   // the tile's MMAs have read its patch
+      pstage += G;
+      while (pstage >= S) pstage -= S;
+      if (etr) p.trace[i * 8 + 6] = clock64();
       uint32_t acc[32];
-      tmem_ld_32x32b_x32(tmem_base + (uint32_t(q4 * 32) << 16) + uint32_t(buf * BLOCK_N + g * 32), acc);
-      tmem_ld_wait();
+      if (!(p.dbg_skip & 4)) {
+        tmem_ld_32x32b_x32(tmem_base + (uint32_t(q4 * 32) << 16) + uint32_t(buf * BLOCK_N + g * 32), acc);
+        tmem_ld_wait();
+      }
       tc_fence_before();
       mbar_arrive(smem_u32(&tmem_empty[buf]));
       uint8_t* stage_out = outbuf + buf * kChunkBytes;
       uint4* out_row = reinterpret_cast<uint4*>(stage_out + row * 128);
 #pragma unroll
-      for (int jj = 0; jj < 4; ++jj) {
+      for (int jj = 0; jj < 4 && !(p.dbg_skip & 4); ++jj) {
         const int j = g * 4 + jj;
         const float4 b0 = *reinterpret_cast<const float4*>(s_bias + j * 8);
         const float4 b1 = *reinterpret_cast<const float4*>(s_bias + j * 8 + 4);
@@ -1141,7 +1193,8 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
       }
       fence_proxy_async_smem();
       asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
-      if (p.pool) {
+      if (p.dbg_skip & 2) {
+      } else if (p.pool) {
         // 3 x 7 pooled pixels x eight 16-byte channel chunks = 168 work items for the group's 256 threads; the conv
         // tile sits in the staging buffer as 128 rows (y*8 + x) of 128 swizzled bytes
         const int tg = int(threadIdx.x) - 64 - grp * kEpiThreads;
@@ -1186,6 +1239,7 @@ stem7x7_kernel(const __grid_constant__ CUtensorMap tmPatch, const __grid_constan
         tma_store_4d(&tmOut, smem_u32(stage_out), n_tile * BLOCK_N, x0, y0, n);   // box {64 ch, 8, 16, 1}
         tma_store_commit();
       }
+      if (etr) p.trace[i * 8 + 7] = clock64();
     }
     if (store_thread) tma_store_wait_read();
   }
@@ -2002,17 +2056,24 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
     sp.relu = e.relu;
     sp.bias = e.bias;
     sp.w_packed = w_packed;
+    if (const char* v = std::getenv("B200RN_STEM_DBG")) sp.dbg_skip = std::atoi(v);
+    if (std::getenv("B200RN_DBG_TRACE")) {
+      cudaMalloc(&sp.trace, 64 * 8 * sizeof(unsigned long long));
+      cudaMemset(sp.trace, 0, 64 * 8 * sizeof(unsigned long long));
+    }
     const int sms = sm_count();
     int grid = std::min(sp.total_tiles, sms);
     grid = std::max(sp.n_tiles, (grid / sp.n_tiles) * sp.n_tiles);
     {
-      // with the fused pool a tile's epilogue (conv tile -> staging -> 3x3 max -> global) is a ~4000-cycle chain; three
-      // groups keep three tiles in flight (B200RN_STEM_GROUPS overrides)
+      // a tile's epilogue (TMEM -> staging -> store: ~2300 cycles; with the fused pool ~4000) is a longer chain than its
+      // 14 MMAs (~630 cycles): three groups keep three tiles in flight (0.132 -> 0.119 ms at batch 256 against two;
+      // B200RN_STEM_GROUPS overrides)
       const char* ge = std::getenv("B200RN_STEM_GROUPS");
-      sp.groups = ge ? std::max(2, std::min(3, std::atoi(ge))) : (e.pool_fused ? 3 : 2);
+      sp.groups = ge ? std::max(2, std::min(3, std::atoi(ge))) : 3;
     }
     const uint32_t fixed = 1024u + kStemWBytes + uint32_t(sp.groups) * kChunkBytes + 3u * 64u * 4 + 8u * (2 * 16 + 9) + 64;
     sp.stages = std::max(2, std::min(16, int((227u * 1024 - fixed) / kStemStageBytes)));
+    if (const char* v = std::getenv("B200RN_STEM_STAGES")) sp.stages = std::max(2, std::min(sp.stages, std::atoi(v)));
     pl->smem_bytes = fixed + uint32_t(sp.stages) * kStemStageBytes;
     pl->grid = grid;
     std::string smsg;
@@ -2330,6 +2391,22 @@ void umma_conv_plan_set_out_f32(UmmaConvPlan* p, float* out_f32) {
 }
 
 void umma_conv_plan_destroy(UmmaConvPlan* p) {
+  if (p && p->stem2 && p->sp.trace) {
+    std::vector<unsigned long long> h(64 * 8);
+    cudaDeviceSynchronize();
+    cudaMemcpy(h.data(), p->sp.trace, h.size() * 8, cudaMemcpyDeviceToHost);
+    const unsigned long long t0 = h[0];
+    std::fprintf(stderr, "stem kernel CTA 0 (groups %d stages %d), per tile: producer slot free | MMA top | waits done | MMAs issued | committed | "
+                         "epilogue top | accumulator full | epilogue end (cycles)\n", p->sp.groups, p->sp.stages);
+    for (int i = 0; i < 40; ++i) {
+      std::fprintf(stderr, "tile %2d:", i);
+      for (int k = 0; k < 8; ++k) std::fprintf(stderr, " %7lld", h[size_t(i) * 8 + k] ? (long long)(h[size_t(i) * 8 + k] - t0) : -1LL);
+      std::fprintf(stderr, "\n");
+    }
+    cudaFree(p->sp.trace);
+    delete p;
+    return;
+  }
   if (p && p->wide && p->wp.trace) {
     std::vector<unsigned long long> h(96 * 8);
     cudaDeviceSynchronize();
