@@ -249,4 +249,6 @@ def test_native_load_generator_against_the_worker(worker):
         assert j["ok"] == n and j["failed"] == 0 and j["req_per_s"] > 0 and j["p50_ms"] <= j["p99_ms"], j
     after = requests.get(worker + "/health", timeout=2).json()
     assert after["total_requests"] - before["total_requests"] == 248
-    assert after["cache_hits"] - before["cache_hits"] >= 180          # 200 small requests over 10 distinct vectors
+    # 200 small requests over 10 distinct vectors; the four threads ask for the same key at the same moment, so each key
+    # can miss up to four times before its first put lands
+    assert after["cache_hits"] - before["cache_hits"] >= 160
