@@ -1450,6 +1450,7 @@ conv_dualm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #include "conv_tail.cuh"
 #include "conv_wide.cuh"
 #include "conv_pair.cuh"
+#include "conv_pairwide.cuh"
 #include "conv_tf32.cuh"
 
 // ---- host side --------------------------------------------------------------------------------
@@ -1530,6 +1531,7 @@ struct UmmaConvPlan {
   int stem2 = 0;          // stem routed to stem7x7_kernel (tmA = patch map, tmOut = {64, 8, 16, 1} store map)
   Stem2Params sp;
   int wide = 0;           // epilogue-bound 1x1 conv with a 256-wide N tile routed to conv_wide_kernel
+  int pairwide = 0;       // ... and, when its K is large and its weights stream, run as a CTA pair (conv_pairwide_kernel)
   WideParams wp;
   int tail = 0;           // 1x1 conv + residual fused with the following 1x1 conv (conv_tail_kernel)
   TailParams tp;
@@ -1891,8 +1893,24 @@ static cudaError_t launch_wide(const UmmaConvPlan* pl, cudaStream_t s) {
   return launch_pdl(kern, pl->grid, kWideThreads, pl->smem_bytes, s, pl->tmA, pl->tmA2, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->wp);
 }
 
+template <typename T>
+static cudaError_t launch_pairwide(const UmmaConvPlan* pl, cudaStream_t s) {
+  auto kern = conv_pairwide_kernel<T, 256>;
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    configured_device = dev;
+  }
+  // the cluster shape (2,1,1) is part of the kernel (__cluster_dims__); the grid is a multiple of 2 x n_tiles
+  return launch_pdl(kern, pl->grid, kPairWideThreads, pl->smem_bytes, s, pl->tmA, pl->tmA2, pl->tmW, pl->tmRes, pl->tmOut, pl->tmAct, pl->wp);
+}
+
 cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
   const bool bf = pl->dt == DType::BF16;
+  if (pl->pairwide) return bf ? launch_pairwide<__nv_bfloat16>(pl, s) : launch_pairwide<__half>(pl, s);
   if (pl->wide) {
     if (pl->block_n == 128) return bf ? launch_wide<__nv_bfloat16, 128>(pl, s) : launch_wide<__half, 128>(pl, s);
     return bf ? launch_wide<__nv_bfloat16, 256>(pl, s) : launch_wide<__half, 256>(pl, s);
@@ -1924,15 +1942,37 @@ cudaError_t launch_conv_umma(const UmmaConvPlan* pl, cudaStream_t s) {
   return bf ? launch_epi<__nv_bfloat16, 256, 128>(pl, s) : launch_epi<__half, 256, 128>(pl, s);
 }
 
-UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in, const void* w_packed,
-                                    const Epilogue& e, int stem_mode, char* err, size_t errcap) {
+// A 1x1 / stride-1 / pad-0 conv is a plain GEMM over the B*H*W pixels, and NHWC keeps those pixels' channel rows at a
+// constant pitch: such a layer is planned as ONE image of 1 x (B*H*W) pixels, so that an M tile is 128 CONSECUTIVE
+// rows of every tensor it touches (input, second input, residual, outputs).  With the spatial patches choose_patch
+// otherwise finds for 14x14 and 7x7 maps (2 x 2 pixels x 32 images, 1 pixel x 128 images) every 128- or 256-byte piece
+// of a tile lies in a different image, 100-400 KB apart, and the residual / output traffic of stages 3 and 4 ran at
+// half of the DRAM rate; flattened tiles also always fill all 128 rows.  B200RN_FLATTEN=0 keeps the spatial patches.
+static bool flatten_1x1(ConvGeom& g, Epilogue& e, int stem_mode) {
+  const char* fe = std::getenv("B200RN_FLATTEN");
+  if (fe && fe[0] == '0') return false;
+  if (stem_mode || g.kh != 1 || g.kw != 1 || g.stride != 1 || g.pad != 0 || g.H * g.W <= 1) return false;
+  if (e.in_b && (e.in_b_stride != 1 || e.in_b_h != g.H || e.in_b_w != g.W)) return false;
+  if (e.out_f32) return false;
+  const long long px = 1LL * g.B * g.H * g.W;
+  if (px > 0x7fffffffLL) return false;
+  g.B = 1; g.H = 1; g.W = int(px); g.Ho = 1; g.Wo = int(px);
+  if (e.in_b) { e.in_b_h = 1; e.in_b_w = int(px); }
+  return true;
+}
+
+UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g_in, const void* in, const void* w_packed,
+                                    const Epilogue& e_in, int stem_mode, char* err, size_t errcap) {
   auto failmsg = [&](const std::string& m) -> UmmaConvPlan* {
     if (err && errcap) std::snprintf(err, errcap, "%s", m.c_str());
     return nullptr;
   };
   char why[200];
   if (dt == DType::F32) return failmsg("tensor-core conv needs a 16-bit activation type");
-  if (!umma_conv_supported(g, stem_mode, why, sizeof why)) return failmsg(why);
+  if (!umma_conv_supported(g_in, stem_mode, why, sizeof why)) return failmsg(why);
+  ConvGeom g = g_in;
+  Epilogue e = e_in;
+  flatten_1x1(g, e, stem_mode);
   auto pl = new UmmaConvPlan();
   pl->dt = dt; pl->g = g; pl->stem = stem_mode;
   UmmaParams& p = pl->p;
@@ -2233,13 +2273,26 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       else if (bstat_ok && Ktot == 256 && g.Cout % 128 == 0) { wp.b_stationary = 1; N = 128; }
       pl->block_n = N;
       wp.n_tiles = g.Cout / N;
-      const char* senv = std::getenv("B200RN_WIDE_STAGES");
+      // Large K with streamed weights and a residual / two-input epilogue: one 256 x 256 tile per CTA pair
+      // (conv_pairwide_kernel): half the weight bytes per SM and stage, so four stages fit beside the rings.
+      // Measured at batch 256 (wide -> pair-wide): see DESIGN.md 4.3.  B200RN_PAIRWIDE=0 turns it off,
+      // B200RN_PAIRWIDE_MINK (default 8) is the smallest K-block count, B200RN_PAIRWIDE_STAGES the stage count.
+      {
+        const char* pwe = std::getenv("B200RN_PAIRWIDE");
+        const char* pwk = std::getenv("B200RN_PAIRWIDE_MINK");
+        const int pw_min_k = pwk ? std::max(2, std::atoi(pwk)) : 8;
+        pl->pairwide = pair_enabled() && !(pwe && pwe[0] == '0') && !wp.b_stationary && N == 256 && !deep && (p.has_res || e.in_b) &&
+                       wp.num_k_iters >= pw_min_k && wp.m_tiles >= 2 && sm_count() >= 2 * wp.n_tiles;
+      }
+      const char* senv = std::getenv(pl->pairwide ? "B200RN_PAIRWIDE_STAGES" : "B200RN_WIDE_STAGES");
       const uint32_t slab = wp.b_stationary ? uint32_t(wp.num_k_iters) * uint32_t(N) * 128u : 0u;
-      const uint32_t stage_bytes = wp.b_stationary ? uint32_t(kTileM) * 128u : uint32_t(kTileM + N) * 128u;
-      wp.stages = senv ? std::max(2, std::min(4, std::atoi(senv)))
+      const uint32_t stage_bytes = pl->pairwide ? uint32_t(kTileM + N / 2) * 128u
+                                                : (wp.b_stationary ? uint32_t(kTileM) * 128u : uint32_t(kTileM + N) * 128u);
+      wp.stages = senv ? std::max(2, std::min(pl->pairwide ? 5 : 4, std::atoi(senv)))
+                       : pl->pairwide ? 4
                        : (wp.b_stationary ? std::max(2, std::min(4, wp.num_k_iters + 1))
                                            : ((deep && !p.has_res) ? 4 : ((e.in_b && wp.num_k_iters >= wide_s3_min_k()) ? 3 : 2)));
-      const uint32_t fixed = 1024u + (p.has_act ? 3u : 1u) * uint32_t(N) * 4 + 8u * (2 * 4 + 4 + 33) + 64;
+      const uint32_t fixed = 1024u + (p.has_act ? 3u : 1u) * uint32_t(N) * 4 + 8u * (2 * 5 + 4 + 33) + 64;
       const int slots = (int(227u * 1024) - int(fixed) - int(slab) - int(uint32_t(wp.stages) * stage_bytes)) / int(kChunkBytes);
       const bool use_r = p.has_res || p.has_out;
       if (use_r && p.has_act) { wp.c_slots = std::max(2, slots * 3 / 7); wp.r_slots = slots - wp.c_slots; }
@@ -2251,6 +2304,12 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       const long total = long(wp.m_tiles) * wp.n_tiles;
       int grid = int(std::min<long>(total, sms));
       grid = std::max(wp.n_tiles, (grid / wp.n_tiles) * wp.n_tiles);
+      if (pl->pairwide) {                       // clusters of two CTAs; the cluster count is a multiple of the N tile count
+        const long pair_total = long((wp.m_tiles + 1) / 2) * wp.n_tiles;
+        int clusters = int(std::min<long>(pair_total, sms / 2));
+        clusters = std::max(wp.n_tiles, (clusters / wp.n_tiles) * wp.n_tiles);
+        grid = 2 * clusters;
+      }
       pl->grid = grid;
       pl->smem_bytes = fixed + slab + uint32_t(wp.stages) * stage_bytes +
                        uint32_t((use_r ? wp.r_slots : 0) + (p.has_act ? wp.c_slots : 0)) * kChunkBytes;
@@ -2268,7 +2327,7 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       if (wok) {
         uint64_t wd[2] = {uint64_t(Ktot), uint64_t(g.Cout)};
         uint64_t ws[1] = {uint64_t(Ktot) * 2};
-        uint32_t wb[2] = {64, uint32_t(N)};
+        uint32_t wb[2] = {64, uint32_t(pl->pairwide ? N / 2 : N)};     // a CTA of a pair stages half of the weight tile
         uint32_t we[2] = {1, 1};
         wok = encode(&pl->tmW, dt, 2, w_packed, wd, ws, wb, we, false, wmsg);
       }
@@ -2278,8 +2337,8 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g, const void* in,
       if (wok) wok = encode_act(&pl->tmRes, dt, e.residual ? e.residual : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, wmsg);
       if (!wok) { delete pl; return failmsg(wmsg); }
       if (std::getenv("B200RN_VERBOSE"))
-        std::fprintf(stderr, "[b200rn] conv 1x1 s%d %d->%d @%dx%d B%d: wide-epilogue N=%d bstat=%d patch=%dx%dx%d m_tiles=%d n_tiles=%d grid=%d stages=%d r_slots=%d c_slots=%d smem=%u\n",
-                     g.stride, g.Cin, g.Cout, g.H, g.W, g.B, N, wp.b_stationary, bw, bh, bn, wp.m_tiles, wp.n_tiles, grid, wp.stages,
+        std::fprintf(stderr, "[b200rn] conv 1x1 s%d %d->%d @%dx%d B%d: %swide-epilogue N=%d bstat=%d patch=%dx%dx%d m_tiles=%d n_tiles=%d grid=%d stages=%d r_slots=%d c_slots=%d smem=%u\n",
+                     g.stride, g.Cin, g.Cout, g.H, g.W, g.B, pl->pairwide ? "pair-" : "", N, wp.b_stationary, bw, bh, bn, wp.m_tiles, wp.n_tiles, grid, wp.stages,
                      wp.r_slots, wp.c_slots, pl->smem_bytes);
       return pl;
     }
@@ -2554,12 +2613,15 @@ static bool encode_act_f32(CUtensorMap* m, const void* base, int B, int H, int W
   return encode_f32(m, 4, base, dims, str, box, estr, err);
 }
 
-Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g, const float* in, const float* w_hi, const float* w_lo, const Epilogue& e,
+Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g_in, const float* in, const float* w_hi, const float* w_lo, const Epilogue& e_in,
                                     char* err, size_t errcap, int stem) {
   auto failmsg = [&](const std::string& m) -> Tf32ConvPlan* {
     if (err && errcap) std::snprintf(err, errcap, "%s", m.c_str());
     return nullptr;
   };
+  ConvGeom g = g_in;
+  Epilogue e = e_in;
+  if (!e.in_b && !e.out_f32) flatten_1x1(g, e, stem);       // 1x1 / stride-1 convs: M tile = 128 consecutive pixel rows
   if (stem ? !tf32_stem_supported(g) : !tf32_conv_supported(g))
     return failmsg(stem ? "3xTF32 stem needs a 7x7/2 pad-3 conv on a 4-channel input of even height with Cout % 64 == 0"
                         : "3xTF32 conv needs Cin % 32 == 0, Cout % 64 == 0, a square filter and stride 1 or 2");

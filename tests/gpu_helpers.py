@@ -262,6 +262,16 @@ CONV_CASES = [
     ("pair 1x1 1024->256 @14 B256 (196 items)", dict(B=256, H=14, W=14, Cin=1024, Cout=256, k=1, stride=1, pad=0, relu=1)),
     ("pair 3x3 s2 256->256 @28 B70", dict(B=70, H=28, W=28, Cin=256, Cout=256, k=3, stride=2, pad=1, relu=1)),
     ("pair 1x1 2048->512 @7 B200 (two N tiles)", dict(B=200, H=7, W=7, Cin=2048, Cout=512, k=1, stride=1, pad=0, relu=1)),
+    # CTA-pair kernel with the wide epilogue (conv_pairwide_kernel: K >= 512, streamed weights, residual): many tiles per
+    # cluster (rings and both accumulators reused), an odd number of M tiles, act-only / raw-only outputs, K = 1024
+    ("pairwide 512->2048 @7 B256 res raw+act (392 items)", dict(B=256, H=7, W=7, Cin=512, Cout=2048, k=1, stride=1, pad=0,
+                                                                residual=True, want_out=True, want_act=True)),
+    ("pairwide 512->1024 @14 B3 res raw (odd M tiles)", dict(B=3, H=14, W=14, Cin=512, Cout=1024, k=1, stride=1, pad=0,
+                                                             residual=True)),
+    ("pairwide 1024->512 @14 B40 res act-only no-relu", dict(B=40, H=14, W=14, Cin=1024, Cout=512, k=1, stride=1, pad=0,
+                                                             residual=True, want_out=False, want_act=True, act_relu=0)),
+    ("pairwide 512->256 @13x9 B5 ragged res raw+act relu", dict(B=5, H=13, W=9, Cin=512, Cout=256, k=1, stride=1, pad=0, relu=1,
+                                                                residual=True, want_out=True, want_act=True)),
     # large-K plain 1x1 conv with at least two waves of tiles: the wide kernel's four-stage configuration
     ("deep 512->256 @28 B50 (306 tiles)", dict(B=50, H=28, W=28, Cin=512, Cout=256, k=1, stride=1, pad=0, relu=1)),
 ]

@@ -23,6 +23,42 @@ def test_conv2d(dtype, name, kw, monkeypatch):
             assert r[key]["viol"] == 0, (name, key, r[key])
 
 
+ONE_BY_ONE_CASES = [c for c in gh.CONV_CASES if c[1]["k"] == 1 and c[1]["stride"] == 1 and c[1]["pad"] == 0]
+
+
+@pytest.mark.parametrize("dtype", [1, 2], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("name,kw", ONE_BY_ONE_CASES, ids=[c[0] for c in ONE_BY_ONE_CASES])
+def test_conv1x1_with_spatial_patches(dtype, name, kw, monkeypatch):
+    """1x1 / stride-1 convs are planned as one row of B*H*W pixels (an M tile = 128 consecutive rows); B200RN_FLATTEN=0
+    keeps the spatial patch tiling every other conv uses.  Both must give the same answers."""
+    monkeypatch.setenv("B200RN_FLATTEN", "0")
+    if name.startswith("wide"):
+        monkeypatch.setenv("B200RN_WIDE", "2")
+    if name.startswith("pair"):
+        monkeypatch.setenv("B200RN_PAIR", "2")
+    r = gh.conv_case(dtype, **kw)
+    assert r["rc"] == 0, r["msg"]
+    for key in ("out", "act"):
+        if key in r:
+            assert r[key]["viol"] == 0, (name, key, r[key])
+
+
+PAIRWIDE_CASES = [c for c in gh.CONV_CASES if c[0].startswith("pairwide") or c[0].startswith("wide 512->2048")]
+
+
+@pytest.mark.parametrize("dtype", [1, 2], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("name,kw", PAIRWIDE_CASES, ids=[c[0] for c in PAIRWIDE_CASES])
+def test_conv2d_large_k_residual_on_one_cta(dtype, name, kw, monkeypatch):
+    """The same large-K residual shapes with the CTA-pair route off (B200RN_PAIRWIDE=0): conv_wide_kernel with two
+    48 KB operand stages, the path these layers took before conv_pairwide_kernel."""
+    monkeypatch.setenv("B200RN_PAIRWIDE", "0")
+    r = gh.conv_case(dtype, **kw)
+    assert r["rc"] == 0, r["msg"]
+    for key in ("out", "act"):
+        if key in r:
+            assert r[key]["viol"] == 0, (name, key, r[key])
+
+
 @pytest.mark.parametrize("name,kw", gh.FP32_CASES, ids=[c[0] for c in gh.FP32_CASES])
 def test_conv2d_exact_mode_shapes(name, kw):
     r = gh.conv_case(0, **kw)
@@ -70,7 +106,9 @@ def test_conv2d_large_k_without_cta_pairs(dtype, name, kw, monkeypatch):
     monkeypatch.setenv("B200RN_PAIR", "0")
     r = gh.conv_case(dtype, **kw)
     assert r["rc"] == 0, r["msg"]
-    assert r["out"]["viol"] == 0, (name, r["out"])
+    for key in ("out", "act"):
+        if key in r:
+            assert r[key]["viol"] == 0, (name, key, r[key])
 
 
 @pytest.mark.parametrize("dtype", [0, 1, 2], ids=["fp32", "bf16", "fp16"])
@@ -119,7 +157,9 @@ TWO_INPUT_CASES = [
 
 @pytest.mark.parametrize("dtype", [1, 2], ids=["bf16", "fp16"])
 @pytest.mark.parametrize("case", TWO_INPUT_CASES, ids=["%dx%dx%d_%d+%ds%d_%d" % c for c in TWO_INPUT_CASES])
-def test_conv1x1_two_input(dtype, case):
+@pytest.mark.parametrize("pairwide", ["1", "0"], ids=["pair", "one-cta"])
+def test_conv1x1_two_input(dtype, case, pairwide, monkeypatch):
+    monkeypatch.setenv("B200RN_PAIRWIDE", pairwide)      # K >= 512 shapes: conv_pairwide_kernel or conv_wide_kernel
     B, H, W, Cin, Cin_b, sb, Cout = case
     r = gh.two_input_case(dtype, B, H, W, Cin, Cin_b, sb, Cout=Cout)
     assert r["rc"] == 0, r["msg"]
