@@ -23,7 +23,8 @@ conv_pairwide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   constexpr int kChunks = N / 64;
   constexpr uint32_t A_BYTES = kTileM * 128;
   constexpr uint32_t BH_BYTES = (N / 2) * 128;              // this CTA's half of the weight tile
-  constexpr uint32_t STAGE_BYTES = A_BYTES + BH_BYTES;
+  // a stage holds an A tile and, unless the pair's weight slab is stationary, this CTA's half of the matching B tile
+  const uint32_t STAGE_BYTES = p.b_stationary ? A_BYTES : A_BYTES + BH_BYTES;
 
   extern __shared__ uint8_t smem_raw[];
   // identical carve-up in both CTAs (the MMA and the multicast commits address the peer by the same offsets)
@@ -31,7 +32,8 @@ conv_pairwide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   const int S = p.stages, SR = p.r_slots, SC = p.c_slots;
   const bool use_r = p.has_res || p.has_out;
   const int SS = use_r ? SR : SC;
-  uint8_t* pipe = smem;
+  uint8_t* bstat = smem;                          // [num_k_iters x half B tile] when b_stationary
+  uint8_t* pipe = bstat + (p.b_stationary ? p.num_k_iters * BH_BYTES : 0);
   uint8_t* r_ring = pipe + S * STAGE_BYTES;
   uint8_t* c_ring = r_ring + (use_r ? SR : 0) * kChunkBytes;
   float* s_bias = reinterpret_cast<float*>(c_ring + (p.has_act ? SC : 0) * kChunkBytes);
@@ -46,7 +48,8 @@ conv_pairwide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   uint64_t* r_empty = r_full + 8;            // [SR]  store warp -> residual TMA
   uint64_t* c_free = r_empty + 8;            // [SC]  store warp -> epilogue
   uint64_t* staged = c_free + 8;             // [SS]  epilogue -> store warp (8 warp arrivals: the owning group)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(staged + 8);
+  uint64_t* bstat_bar = staged + 8;          // [1]   (used in the leader) both CTAs' stationary weights landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bstat_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -72,6 +75,7 @@ conv_pairwide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       mbar_init(smem_u32(&r_full[i]), 1); mbar_init(smem_u32(&r_empty[i]), 1);
       mbar_init(smem_u32(&c_free[i]), 1); mbar_init(smem_u32(&staged[i]), kWideGroupWarps);
     }
+    mbar_init(smem_u32(bstat_bar), 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc_pair(smem_u32(tmem_slot), 2 * N);
@@ -96,17 +100,23 @@ conv_pairwide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       int stage = 0;
       uint32_t phase = 0;
       const int bcol = col0 + int(rank) * (N / 2);
+      if (p.b_stationary && my_tiles > 0) {      // the pair's N tile never changes: each CTA fetches its half of the slab once
+        const uint32_t bb_local = smem_u32(bstat_bar);
+        const uint32_t bb = mapa_cluster(bb_local, 0);
+        if (rank == 0) mbar_expect_tx(bb_local, 2u * uint32_t(p.num_k_iters) * BH_BYTES);
+        for (int it = 0; it < p.num_k_iters; ++it) tma_load_2d_pair(smem_u32(bstat + it * BH_BYTES), &tmW, bb, it * 64, bcol);
+      }
       for (int i = 0; i < my_tiles; ++i) {
         const WideTile tc = my_tile(i);
         for (int it = 0; it < p.num_k_iters; ++it) {
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
           const uint32_t fb_local = smem_u32(&full_bar[stage]);
           const uint32_t fb = mapa_cluster(fb_local, 0);
-          if (rank == 0) mbar_expect_tx(fb_local, 2 * (p.a_bytes + BH_BYTES));
+          if (rank == 0) mbar_expect_tx(fb_local, p.b_stationary ? 2 * p.a_bytes : 2 * (p.a_bytes + BH_BYTES));
           const uint32_t dst = smem_u32(pipe + stage * STAGE_BYTES);
           if (it < p.k1_iters) tma_load_4d_pair(dst, &tmA, fb, it * 64, tc.w0 * p.stride, tc.h0 * p.stride, tc.n0);
           else tma_load_4d_pair(dst, &tmA2, fb, (it - p.k1_iters) * 64, tc.w0 * p.stride_b, tc.h0 * p.stride_b, tc.n0);
-          tma_load_2d_pair(dst + A_BYTES, &tmW, fb, it * 64, bcol);
+          if (!p.b_stationary) tma_load_2d_pair(dst + A_BYTES, &tmW, fb, it * 64, bcol);
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
       }
@@ -123,8 +133,10 @@ conv_pairwide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     constexpr uint32_t desc_hi = smem_desc_hi<128>();
     if (rank == 0 && elect_one()) {
       const uint32_t pipe_lo = smem_desc_lo(smem_u32(pipe));
+      const uint32_t bstat_lo = smem_desc_lo(smem_u32(bstat));
       int stage = 0;
       uint32_t phase = 0;
+      if (p.b_stationary && my_tiles > 0) mbar_wait(smem_u32(bstat_bar), 0);
       for (int i = 0; i < my_tiles; ++i) {
         const int buf = i & 1;
         mbar_wait(smem_u32(&tmem_empty[buf]), ((uint32_t(i) >> 1) & 1) ^ 1);   // both CTAs' epilogues drained this accumulator
@@ -134,7 +146,7 @@ conv_pairwide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           mbar_wait(smem_u32(&full_bar[stage]), phase);
           tc_fence_after();
           const uint32_t a_lo = pipe_lo + uint32_t(stage) * (STAGE_BYTES >> 4);
-          const uint32_t b_lo = a_lo + (A_BYTES >> 4);
+          const uint32_t b_lo = p.b_stationary ? bstat_lo + uint32_t(it) * (BH_BYTES >> 4) : a_lo + (A_BYTES >> 4);
 #pragma unroll
           for (int k = 0; k < 4; ++k) umma_f16_lo_pair(tmem_d, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (it | k) != 0 ? 1u : 0u);
           umma_commit_pair(smem_u32(&empty_bar[stage]));

@@ -2269,27 +2269,32 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g_in, const void* 
       const bool bstat_ok = !(benv && benv[0] == '0') && !deep;
       int N = kWideN;
       wp.b_stationary = 0;
+      // CTA pair (conv_pairwide_kernel): K >= 512 with streamed weights (half the weight bytes per SM and stage, so three
+      // or four stages fit beside the rings).  Measured at batch 256 (one CTA -> pair): projection blocks of stages 3 / 4
+      // 0.097 -> 0.089 / 0.087 -> 0.075 ms, 512 -> 2048 @7x7 + residual 0.059 -> 0.054 and 0.051 -> 0.046.
+      // Opt-in only (B200RN_PAIRWIDE_BSTAT=1): K = 256 with the pair's 256-wide slab stationary, half in each CTA -- it
+      // halves the A re-reads of the single-CTA form (which drops to N = 128 to keep its slab) but ran the 256 -> 1024
+      // @14x14 residual layers at 0.083-0.089 ms against 0.070: they are bound by the epilogue rings, not the feed.
+      // B200RN_PAIRWIDE=0 turns the pair route off, B200RN_PAIRWIDE_MINK (default 8) is the smallest streamed K-block
+      // count, B200RN_PAIRWIDE_STAGES the stage count.
+      const char* pwe = std::getenv("B200RN_PAIRWIDE");
+      const char* pwk = std::getenv("B200RN_PAIRWIDE_MINK");
+      const char* pwb = std::getenv("B200RN_PAIRWIDE_BSTAT");
+      const int pw_min_k = pwk ? std::max(2, std::atoi(pwk)) : 8;
+      const bool pw_ok = pair_enabled() && !(pwe && pwe[0] == '0') && !deep && (p.has_res || e.in_b) && wp.m_tiles >= 2 &&
+                         sm_count() >= 2 * (g.Cout / kWideN);
       if (bstat_ok && Ktot <= 128) wp.b_stationary = 1;
+      else if (bstat_ok && Ktot == 256 && pw_ok && pwb && pwb[0] == '1') { wp.b_stationary = 1; pl->pairwide = 1; }
       else if (bstat_ok && Ktot == 256 && g.Cout % 128 == 0) { wp.b_stationary = 1; N = 128; }
+      else if (pw_ok && wp.num_k_iters >= pw_min_k) pl->pairwide = 1;
       pl->block_n = N;
       wp.n_tiles = g.Cout / N;
-      // Large K with streamed weights and a residual / two-input epilogue: one 256 x 256 tile per CTA pair
-      // (conv_pairwide_kernel): half the weight bytes per SM and stage, so four stages fit beside the rings.
-      // Measured at batch 256 (wide -> pair-wide): see DESIGN.md 4.3.  B200RN_PAIRWIDE=0 turns it off,
-      // B200RN_PAIRWIDE_MINK (default 8) is the smallest K-block count, B200RN_PAIRWIDE_STAGES the stage count.
-      {
-        const char* pwe = std::getenv("B200RN_PAIRWIDE");
-        const char* pwk = std::getenv("B200RN_PAIRWIDE_MINK");
-        const int pw_min_k = pwk ? std::max(2, std::atoi(pwk)) : 8;
-        pl->pairwide = pair_enabled() && !(pwe && pwe[0] == '0') && !wp.b_stationary && N == 256 && !deep && (p.has_res || e.in_b) &&
-                       wp.num_k_iters >= pw_min_k && wp.m_tiles >= 2 && sm_count() >= 2 * wp.n_tiles;
-      }
       const char* senv = std::getenv(pl->pairwide ? "B200RN_PAIRWIDE_STAGES" : "B200RN_WIDE_STAGES");
-      const uint32_t slab = wp.b_stationary ? uint32_t(wp.num_k_iters) * uint32_t(N) * 128u : 0u;
-      const uint32_t stage_bytes = pl->pairwide ? uint32_t(kTileM + N / 2) * 128u
-                                                : (wp.b_stationary ? uint32_t(kTileM) * 128u : uint32_t(kTileM + N) * 128u);
+      const uint32_t slab = wp.b_stationary ? uint32_t(wp.num_k_iters) * uint32_t(pl->pairwide ? N / 2 : N) * 128u : 0u;
+      const uint32_t stage_bytes = wp.b_stationary ? uint32_t(kTileM) * 128u
+                                                   : uint32_t(kTileM + (pl->pairwide ? N / 2 : N)) * 128u;
       wp.stages = senv ? std::max(2, std::min(pl->pairwide ? 5 : 4, std::atoi(senv)))
-                       : pl->pairwide ? 4
+                       : (pl->pairwide && !wp.b_stationary) ? (p.has_res ? 3 : 4)    // residual layers: the rings need the room more (measured)
                        : (wp.b_stationary ? std::max(2, std::min(4, wp.num_k_iters + 1))
                                            : ((deep && !p.has_res) ? 4 : ((e.in_b && wp.num_k_iters >= wide_s3_min_k()) ? 3 : 2)));
       const uint32_t fixed = 1024u + (p.has_act ? 3u : 1u) * uint32_t(N) * 4 + 8u * (2 * 5 + 4 + 33) + 64;

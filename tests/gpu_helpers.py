@@ -272,6 +272,10 @@ CONV_CASES = [
                                                              residual=True, want_out=False, want_act=True, act_relu=0)),
     ("pairwide 512->256 @13x9 B5 ragged res raw+act relu", dict(B=5, H=13, W=9, Cin=512, Cout=256, k=1, stride=1, pad=0, relu=1,
                                                                 residual=True, want_out=True, want_act=True)),
+    ("pairwide 256->1024 @14 B256 res raw+act (stationary half slabs, 784 items)",
+     dict(B=256, H=14, W=14, Cin=256, Cout=1024, k=1, stride=1, pad=0, residual=True, want_out=True, want_act=True)),
+    ("pairwide 256->256 @9x5 B3 res raw (stationary, one pair, ragged)", dict(B=3, H=9, W=5, Cin=256, Cout=256, k=1, stride=1, pad=0,
+                                                                              residual=True)),
     # large-K plain 1x1 conv with at least two waves of tiles: the wide kernel's four-stage configuration
     ("deep 512->256 @28 B50 (306 tiles)", dict(B=50, H=28, W=28, Cin=512, Cout=256, k=1, stride=1, pad=0, relu=1)),
 ]

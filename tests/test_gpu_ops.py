@@ -16,6 +16,8 @@ def test_conv2d(dtype, name, kw, monkeypatch):
         monkeypatch.setenv("B200RN_WIDE", "2")      # also the residual-free shapes go through conv_wide_kernel
     if name.startswith("pair"):
         monkeypatch.setenv("B200RN_PAIR", "2")      # also Cout = 128 layers go through conv_pair_kernel (N = 128 tile)
+    if "stationary" in name:
+        monkeypatch.setenv("B200RN_PAIRWIDE_BSTAT", "1")   # opt-in form of conv_pairwide_kernel: half slabs kept in each CTA
     r = gh.conv_case(dtype, **kw)
     assert r["rc"] == 0, r["msg"]
     for key in ("out", "act"):
@@ -43,7 +45,7 @@ def test_conv1x1_with_spatial_patches(dtype, name, kw, monkeypatch):
             assert r[key]["viol"] == 0, (name, key, r[key])
 
 
-PAIRWIDE_CASES = [c for c in gh.CONV_CASES if c[0].startswith("pairwide") or c[0].startswith("wide 512->2048")]
+PAIRWIDE_CASES = [c for c in gh.CONV_CASES if c[0].startswith(("pairwide", "wide 512->2048", "wide 256->1024"))]
 
 
 @pytest.mark.parametrize("dtype", [1, 2], ids=["bf16", "fp16"])
