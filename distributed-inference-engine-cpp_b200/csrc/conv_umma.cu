@@ -2255,6 +2255,7 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g_in, const void* 
       wp.has_res = p.has_res; wp.has_out = p.has_out; wp.has_act = p.has_act; wp.relu = p.relu; wp.act_relu = p.act_relu;
       wp.rows = uint32_t(bw * bh * bn); wp.a_bytes = wp.rows * 128u;
       wp.bias = e.bias; wp.act_scale = e.act_scale; wp.act_shift = e.act_shift;
+      if (const char* v = std::getenv("B200RN_WIDE_DBG")) wp.dbg_skip = std::atoi(v);
       if (std::getenv("B200RN_DBG_TRACE")) {
         cudaMalloc(&wp.trace, 96 * 8 * sizeof(unsigned long long));
         cudaMemset(wp.trace, 0, 96 * 8 * sizeof(unsigned long long));
@@ -2300,7 +2301,11 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g_in, const void* 
       const uint32_t fixed = 1024u + (p.has_act ? 3u : 1u) * uint32_t(N) * 4 + 8u * (2 * 5 + 4 + 33) + 64;
       const int slots = (int(227u * 1024) - int(fixed) - int(slab) - int(uint32_t(wp.stages) * stage_bytes)) / int(kChunkBytes);
       const bool use_r = p.has_res || p.has_out;
-      if (use_r && p.has_act) { wp.c_slots = std::max(2, slots * 3 / 7); wp.r_slots = slots - wp.c_slots; }
+      if (use_r && p.has_act) {
+        wp.c_slots = std::max(2, slots * 3 / 7);
+        if (const char* ce = std::getenv("B200RN_WIDE_CSLOTS")) wp.c_slots = std::max(2, std::min(slots - 2, std::atoi(ce)));
+        wp.r_slots = slots - wp.c_slots;
+      }
       else if (use_r) wp.r_slots = slots;
       else wp.c_slots = slots;
       wp.r_slots = std::min(8, wp.r_slots); wp.c_slots = std::min(8, wp.c_slots);

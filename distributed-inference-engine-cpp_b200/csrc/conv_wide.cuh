@@ -34,6 +34,8 @@ struct WideParams {
   const float* act_scale;
   const float* act_shift;
   unsigned long long* trace;   // timeline experiment (B200RN_DBG_TRACE): CTA 0; [0..31] MMA thread per tile, [32..] epilogue groups per chunk
+  int dbg_skip;                // timing experiments (B200RN_WIDE_DBG; conv_wide_kernel only): 1 no MMAs, 2 no epilogue arithmetic / staging
+                               // writes, 4 no TMA stores, 8 no residual loads, 16 no operand loads, 32 no TMEM read
 };
 
 struct WideTile { int w0, h0, n0; };
@@ -131,6 +133,7 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int it = 0; it < p.num_k_iters; ++it) {
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
           const uint32_t fb = smem_u32(&full_bar[stage]);
+          if (p.dbg_skip & 16) { mbar_arrive(fb); if (++stage == S) { stage = 0; phase ^= 1; } continue; }
           mbar_expect_tx(fb, p.b_stationary ? p.a_bytes : p.a_bytes + B_BYTES);
           const uint32_t a_dst = smem_u32(pipe + stage * STAGE_BYTES);
           if (it < p.k1_iters) {
@@ -170,7 +173,8 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint32_t a_lo = pipe_lo + uint32_t(stage) * (STAGE_BYTES >> 4);
           const uint32_t b_lo = p.b_stationary ? bstat_lo + uint32_t(it) * (B_BYTES >> 4) : a_lo + (A_BYTES >> 4);
 #pragma unroll
-          for (int k = 0; k < 4; ++k) umma_f16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (it | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < 4; ++k)
+            if (!(p.dbg_skip & 1)) umma_f16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (it | k) != 0 ? 1u : 0u);
           umma_commit(smem_u32(&empty_bar[stage]));
           if (it + 1 == p.num_k_iters) umma_commit(smem_u32(&tmem_full[buf]));
           if (++stage == S) { stage = 0; phase ^= 1; }
@@ -186,8 +190,8 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int c = 0; c < kChunks; ++c, ++cc) {
           const uint32_t slot = use_r ? cc % uint32_t(SR) : 0u, cslot = p.has_act ? cc % uint32_t(SC) : 0u;
           mbar_wait(smem_u32(&staged[cc % uint32_t(SS)]), (cc / uint32_t(SS)) & 1);
-          if (p.has_out) tma_store_4d(&tmOut, smem_u32(r_ring + slot * kChunkBytes), col0 + c * 64, tc.w0, tc.h0, tc.n0);
-          if (p.has_act) tma_store_4d(&tmAct, smem_u32(c_ring + cslot * kChunkBytes), col0 + c * 64, tc.w0, tc.h0, tc.n0);
+          if (p.has_out && !(p.dbg_skip & 4)) tma_store_4d(&tmOut, smem_u32(r_ring + slot * kChunkBytes), col0 + c * 64, tc.w0, tc.h0, tc.n0);
+          if (p.has_act && !(p.dbg_skip & 4)) tma_store_4d(&tmAct, smem_u32(c_ring + cslot * kChunkBytes), col0 + c * 64, tc.w0, tc.h0, tc.n0);
           tma_store_commit();
           tma_store_wait_read();
           if (use_r) mbar_arrive(smem_u32(&r_empty[slot]));
@@ -214,7 +218,7 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint32_t slot = cc % uint32_t(SR);
           mbar_wait(smem_u32(&r_empty[slot]), ((cc / uint32_t(SR)) & 1) ^ 1);
           const uint32_t bar = smem_u32(&r_full[slot]);
-          if (p.has_res) {
+          if (p.has_res && !(p.dbg_skip & 8)) {
             mbar_expect_tx(bar, p.rows * 128u);
             tma_load_4d(smem_u32(r_ring + slot * kChunkBytes), &tmRes, bar, col0 + c * 64, tc.w0, tc.h0, tc.n0);
           } else {
@@ -261,7 +265,7 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tc_fence_after();
         if (tr) trc[1] = clock64();
         uint32_t acc[32];
-        tmem_ld_32x32b_x32(lane_addr + uint32_t(buf * N + c * 64 + g * 32), acc);
+        if (!(p.dbg_skip & 32)) tmem_ld_32x32b_x32(lane_addr + uint32_t(buf * N + c * 64 + g * 32), acc);
         const uint32_t raw_row = smem_u32(r_ring + slot * kChunkBytes) + row_off;
         const uint32_t act_row = smem_u32(c_ring + cslot * kChunkBytes) + row_off;
         const uint32_t pcol = uint32_t(c * 64 + g * 32) * 4;       // byte offset of this thread's first channel in the parameter rows
@@ -277,7 +281,7 @@ conv_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (lane == 0) mbar_arrive(smem_u32(&tmem_empty[buf]));
         }
 #pragma unroll
-        for (int jj = 0; jj < 4; ++jj) {
+        for (int jj = 0; jj < 4 && !(p.dbg_skip & 2); ++jj) {
           const uint32_t slot16 = uint32_t(((g * 4 + jj) ^ sw) << 4);   // SWIZZLE_128B: 16-byte chunk index XOR (row mod 8)
           const float4 b0 = lds_f4(s_bias_a + pcol + jj * 32), b1 = lds_f4(s_bias_a + pcol + jj * 32 + 16);
           float v[8];
