@@ -15,9 +15,11 @@
 // buffers and the epilogue warps add every finished chunk into fp32 REGISTERS (N/2 per thread) with properly rounded
 // adds while the next chunk is being multiplied.  LO is 2^-11 of MAIN, its truncation error is negligible, and it stays
 // in tensor memory for the whole K (double-buffered across tiles).  v = registers + LO + bias.
-// Epilogue (two groups of 8 warps on alternating 32-channel chunks): bias, ReLU, residual (read straight from global
-// memory one chunk ahead, 64 contiguous bytes per thread), raw and/or BN-ReLU'd output staged in swizzled shared memory
-// (one buffer per output and group) and written by TMA stores, 32 channels (128 bytes) per chunk.
+// Epilogue (two groups of 8 warps on alternating 32-channel chunks): bias, ReLU, residual, raw and/or BN-ReLU'd output
+// staged in swizzled shared memory (one buffer per output and group) and written by TMA stores, 32 channels (128 bytes)
+// per chunk.  The residual chunk arrives by TMA in a landing buffer per group, requested one chunk ahead by the group's
+// store thread (res_tma); the first version read it straight from global memory, 64 contiguous bytes per thread, which
+// is 32 separate row pieces per warp instruction and ran the residual layers 10-50 % slower (kept as the fallback).
 // The 7x7/2 stem (3 channels stored as 4) reads a zero-framed fp32 input through a 5-D overlapping view: K block ky is the
 // 8 pixels x 4 channels = 32 contiguous floats at frame row 2y + ky, pixel 2x (the 8th pixel meets zero weights), so the
 // stem is 7 K blocks of the same pipeline.
@@ -40,6 +42,8 @@ struct Tf32Params {
   const float* act_scale;
   const float* act_shift;
   const float* residual;          // fp32 NHWC [B, Ho, Wo, cout] or null
+  int res_tma;                    // residual chunks arrive by TMA in a 16 KB buffer per epilogue group (one chunk ahead) instead of
+                                  // per-thread global loads of 64-byte row pieces
 };
 
 // kind::tf32 instruction descriptor: D fp32 (bit 4), A and B formats = 2 (TF32), both K-major, N >> 3, M >> 4
@@ -69,11 +73,11 @@ __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&v)
 }
 __device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool RES_TMA>
 __global__ void __launch_bounds__(kT32Threads, 1)
 conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmWhi,
                    const __grid_constant__ CUtensorMap tmWlo, const __grid_constant__ CUtensorMap tmOut,
-                   const __grid_constant__ CUtensorMap tmAct, const Tf32Params p) {
+                   const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmRes, const Tf32Params p) {
   constexpr int kChunks = BLOCK_N / 32;               // 32 fp32 channels = one 128-byte staging row
   constexpr int kGroupChunks = kChunks / 2;           // chunks per epilogue group and tile
   constexpr uint32_t A_BYTES = kTileM * 128;          // 128 rows x 32 fp32
@@ -88,7 +92,8 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   uint8_t* pipe = smem;
   uint8_t* outbuf = pipe + S * STAGE_BYTES;                       // raw-output staging: one 16 KB chunk per epilogue group
   uint8_t* actbuf = outbuf + (p.has_out ? 2 * kChunkBytes : 0);   // activated-output staging: one chunk per group
-  uint64_t* bars = reinterpret_cast<uint64_t*>(actbuf + (p.has_act ? 2 * kChunkBytes : 0));
+  uint8_t* resbuf = actbuf + (p.has_act ? 2 * kChunkBytes : 0);   // residual landing buffers: one chunk per group (res_tma)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(resbuf + (RES_TMA ? 2 * kChunkBytes : 0));
   uint64_t* full_bar = bars;                  // [S]  TMA -> transform warps
   uint64_t* xf_bar = full_bar + S;            // [S]  transform warps -> MMA (4 warp arrivals)
   uint64_t* empty_bar = xf_bar + S;           // [S]  MMA -> TMA
@@ -96,7 +101,8 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   uint64_t* main_empty = main_full + 2;       // [2]  epilogue -> MMA (16 warp arrivals): chunk added into registers
   uint64_t* lo_full = main_empty + 2;         // [2]  MMA -> epilogue: a tile's LO accumulator is complete
   uint64_t* lo_empty = lo_full + 2;           // [2]  epilogue -> MMA (16 warp arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(lo_empty + 2);
+  uint64_t* res_full = lo_empty + 2;          // [2]  residual TMA -> epilogue group
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int my_tiles = (int(blockIdx.x) < p.total_tiles) ? (p.total_tiles - 1 - int(blockIdx.x)) / int(gridDim.x) + 1 : 0;
@@ -105,6 +111,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     prefetch_tmap(&tmA); prefetch_tmap(&tmWhi); prefetch_tmap(&tmWlo);
     if (p.has_out) prefetch_tmap(&tmOut);
     if (p.has_act) prefetch_tmap(&tmAct);
+    if (RES_TMA) prefetch_tmap(&tmRes);
     for (int i = 0; i < S; ++i) {
       mbar_init(smem_u32(&full_bar[i]), 1);
       mbar_init(smem_u32(&xf_bar[i]), kT32XfWarps);
@@ -113,6 +120,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&main_full[i]), 1); mbar_init(smem_u32(&main_empty[i]), kT32EpiWarps);
       mbar_init(smem_u32(&lo_full[i]), 1); mbar_init(smem_u32(&lo_empty[i]), kT32EpiWarps);
+      mbar_init(smem_u32(&res_full[i]), 1);
     }
     fence_barrier_init();
   }
@@ -241,6 +249,19 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     const uint32_t out_row = out_stage + uint32_t(row) * 128u, act_row = act_stage + uint32_t(row) * 128u;
     int cc = 0;                                 // this group's running chunk counter
     uint32_t mchunk = 0;                        // running MAIN chunk counter (same sequence as the MMA thread's)
+    const uint32_t res_stage = smem_u32(resbuf) + uint32_t(grp) * kChunkBytes, res_row = res_stage + uint32_t(row) * 128u;
+    const uint32_t res_bar = smem_u32(&res_full[grp]);
+    // res_tma: the group's store thread requests chunk j of tile t into the group's landing buffer (rows past the
+    // batch are zero-filled by TMA); one request is outstanding per group, issued as soon as the previous chunk's
+    // residual has been read by all of the group's threads
+    auto request_residual = [&](int t, int j) {
+      if (t >= my_tiles) return;
+      int rw0, rh0, rn0, rcol0;
+      tile_coord(t, rw0, rh0, rn0, rcol0);
+      mbar_expect_tx(res_bar, p.rows * 128u);
+      tma_load_4d(res_stage, &tmRes, res_bar, rcol0 + (grp + 2 * j) * 32, rw0, rh0, rn0);
+    };
+    if (RES_TMA && store_thread) request_residual(0, 0);
     for (int i = 0; i < my_tiles; ++i) {
       int w0, h0, n0, col0;
       tile_coord(i, w0, h0, n0, col0);
@@ -252,7 +273,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       const float* res_px = p.residual + ((size_t(on) * p.Ho + oy) * p.Wo + ox) * size_t(p.cout) + col0 + g * 16;
       // residual of the group's first chunk: requested now, needed only after the whole K loop
       float4 rv[4];
-      if (p.has_res) {
+      if (p.has_res && !RES_TMA) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           rv[k] = in_range ? __ldg(reinterpret_cast<const float4*>(res_px + grp * 32) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -297,6 +318,14 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         }
         if (store_thread && cc > 0) tma_store_wait_read();   // the group's previous stores have read its staging buffers
         asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
+        if (RES_TMA) {
+          mbar_wait(res_bar, uint32_t(cc) & 1);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint4 r = lds_u4(res_row + uint32_t(((g * 4 + k) ^ sw) << 4));
+            rv[k] = make_float4(__uint_as_float(r.x), __uint_as_float(r.y), __uint_as_float(r.z), __uint_as_float(r.w));
+          }
+        }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           float v[4];
@@ -317,7 +346,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             sts_u4(act_row + slot16, make_uint4(__float_as_uint(a[0]), __float_as_uint(a[1]), __float_as_uint(a[2]), __float_as_uint(a[3])));
           }
         }
-        if (p.has_res && j + 1 < kGroupChunks) {       // the group's next chunk's residual (64 channels further on)
+        if (p.has_res && !RES_TMA && j + 1 < kGroupChunks) {       // the group's next chunk's residual (64 channels further on)
 #pragma unroll
           for (int k = 0; k < 4; ++k)
             rv[k] = in_range ? __ldg(reinterpret_cast<const float4*>(res_px + (c + 2) * 32) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -325,6 +354,8 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         fence_proxy_async_smem();
         asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");
         if (store_thread) {
+          // every thread of the group has read this chunk's residual: the landing buffer takes the next one
+          if (RES_TMA) { if (j + 1 < kGroupChunks) request_residual(i, j + 1); else request_residual(i + 1, 0); }
           if (p.has_out) tma_store_4d(&tmOut, out_stage, col0 + c * 32, w0, h0, n0);
           if (p.has_act) tma_store_4d(&tmAct, act_stage, col0 + c * 32, w0, h0, n0);
           tma_store_commit();

@@ -2557,7 +2557,7 @@ struct Tf32ConvPlan {
   ConvGeom g;
   int block_n;
   Tf32Params p;
-  CUtensorMap tmA, tmWhi, tmWlo, tmOut, tmAct;
+  CUtensorMap tmA, tmWhi, tmWlo, tmOut, tmAct, tmRes;
   uint32_t smem_bytes;
   int grid;
 };
@@ -2660,9 +2660,21 @@ Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g_in, const float* in, const
   if (p.has_act && (!e.act_scale || !e.act_shift)) { delete pl; return failmsg("activated output needs scale and shift"); }
   const uint32_t stage_bytes = 2u * kTileM * 128 + 2u * uint32_t(pl->block_n) * 128;
   // staging: one 16 KB chunk per output and epilogue group
-  const uint32_t fixed = 1024u + 2u * uint32_t(p.has_out + p.has_act) * kChunkBytes + 8u * (3 * 8 + 8) + 64;
+  const uint32_t fixed = 1024u + 2u * uint32_t(p.has_out + p.has_act) * kChunkBytes + 8u * (3 * 8 + 10) + 64;
   p.num_stages = std::max(2, std::min(8, int((227u * 1024 - fixed) / stage_bytes)));
   pl->smem_bytes = fixed + uint32_t(p.num_stages) * stage_bytes;
+  {
+    // Residual by TMA into a 16 KB landing buffer per epilogue group, one chunk ahead, instead of per-thread global loads
+    // of 64-byte row pieces -- also when the two buffers cost an operand stage.  Measured at batch 256 (exact mode):
+    // residual + raw + activated layers 0.79 -> 0.72 (56x56), 0.44 -> 0.385 (28x28), 0.26 -> 0.24 ms (14x14); the
+    // activated-only block ends, which give up their third stage, 0.78 -> 0.51, 0.44 -> 0.30, 0.26 -> 0.22 ms.
+    // B200RN_TF32_RES_TMA: 0 = never, 1 = only where no stage is lost.
+    const char* re = std::getenv("B200RN_TF32_RES_TMA");
+    const int mode = re ? std::atoi(re) : 2;
+    const uint32_t with_res = pl->smem_bytes + 2u * kChunkBytes;
+    if (p.has_res && mode >= 1 && with_res <= 227u * 1024) { p.res_tma = 1; pl->smem_bytes = with_res; }
+    else if (p.has_res && mode >= 2 && p.num_stages > 2) { p.res_tma = 1; --p.num_stages; pl->smem_bytes = fixed + 2u * kChunkBytes + uint32_t(p.num_stages) * stage_bytes; }
+  }
   pl->grid = std::min(p.total_tiles, sm_count());
   std::string msg;
   bool ok;
@@ -2689,18 +2701,19 @@ Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g_in, const float* in, const
   const void* any_out = e.out ? e.out : e.out_act;
   if (ok) ok = encode_act_f32(&pl->tmOut, e.out ? e.out : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
   if (ok) ok = encode_act_f32(&pl->tmAct, e.out_act ? e.out_act : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
+  if (ok) ok = encode_act_f32(&pl->tmRes, p.res_tma ? e.residual : any_out, g.B, g.Ho, g.Wo, g.Cout, bw, bh, bn, 1, msg);
   if (!ok) { delete pl; return failmsg(msg); }
   if (std::getenv("B200RN_VERBOSE"))
-    std::fprintf(stderr, "[b200rn] conv %dx%d s%d %d->%d @%dx%d B%d: 3xTF32 bn=%d patch=%dx%dx%d tiles=%d grid=%d stages=%d smem=%u\n", g.kh, g.kw,
-                 g.stride, g.Cin, g.Cout, g.H, g.W, g.B, pl->block_n, bw, bh, bn, p.total_tiles, pl->grid, p.num_stages, pl->smem_bytes);
+    std::fprintf(stderr, "[b200rn] conv %dx%d s%d %d->%d @%dx%d B%d: 3xTF32 bn=%d patch=%dx%dx%d tiles=%d grid=%d stages=%d res_tma=%d smem=%u\n", g.kh, g.kw,
+                 g.stride, g.Cin, g.Cout, g.H, g.W, g.B, pl->block_n, bw, bh, bn, p.total_tiles, pl->grid, p.num_stages, p.res_tma, pl->smem_bytes);
   return pl;
 }
 
 void tf32_conv_plan_destroy(Tf32ConvPlan* p) { delete p; }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool RES_TMA>
 static cudaError_t launch_tf32_inst(const Tf32ConvPlan* pl, cudaStream_t s) {
-  auto kern = conv_tf32x3_kernel<BLOCK_N>;
+  auto kern = conv_tf32x3_kernel<BLOCK_N, RES_TMA>;
   static thread_local int configured_device = -1;
   int dev = 0;
   cudaGetDevice(&dev);
@@ -2709,11 +2722,13 @@ static cudaError_t launch_tf32_inst(const Tf32ConvPlan* pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  return launch_pdl(kern, pl->grid, kT32Threads, pl->smem_bytes, s, pl->tmA, pl->tmWhi, pl->tmWlo, pl->tmOut, pl->tmAct, pl->p);
+  return launch_pdl(kern, pl->grid, kT32Threads, pl->smem_bytes, s, pl->tmA, pl->tmWhi, pl->tmWlo, pl->tmOut, pl->tmAct, pl->tmRes, pl->p);
 }
 
 cudaError_t launch_conv_tf32(const Tf32ConvPlan* pl, cudaStream_t s) {
-  return pl->block_n == 128 ? launch_tf32_inst<128>(pl, s) : launch_tf32_inst<64>(pl, s);
+  // the residual-by-TMA form is a separate instantiation: it does not keep a chunk's residual in registers across the K loop
+  if (pl->p.res_tma) return pl->block_n == 128 ? launch_tf32_inst<128, true>(pl, s) : launch_tf32_inst<64, true>(pl, s);
+  return pl->block_n == 128 ? launch_tf32_inst<128, false>(pl, s) : launch_tf32_inst<64, false>(pl, s);
 }
 
 cudaError_t umma_take_timeout_flag(unsigned int* flag) {

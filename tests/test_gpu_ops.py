@@ -45,6 +45,21 @@ def test_conv1x1_with_spatial_patches(dtype, name, kw, monkeypatch):
             assert r[key]["viol"] == 0, (name, key, r[key])
 
 
+RESIDUAL_CASES = [c for c in gh.CONV_CASES + gh.FP32_CASES if c[1].get("residual")]
+
+
+@pytest.mark.parametrize("name,kw", RESIDUAL_CASES, ids=[c[0] for c in RESIDUAL_CASES])
+def test_conv2d_exact_mode_residual_from_global(name, kw, monkeypatch):
+    """Exact mode (3 x TF32) with B200RN_TF32_RES_TMA=0: the residual read by per-thread global loads instead of the TMA
+    landing buffers that are the default."""
+    monkeypatch.setenv("B200RN_TF32_RES_TMA", "0")
+    r = gh.conv_case(0, **kw)
+    assert r["rc"] == 0, r["msg"]
+    for key in ("out", "act"):
+        if key in r:
+            assert r[key]["viol"] == 0, (name, key, r[key])
+
+
 PAIRWIDE_CASES = [c for c in gh.CONV_CASES if c[0].startswith(("pairwide", "wide 512->2048", "wide 256->1024"))]
 
 
