@@ -1734,6 +1734,17 @@ static int pair_min_k() {
   const char* v = std::getenv("B200RN_PAIR_MINK");
   return v ? std::max(1, std::atoi(v)) : 8;
 }
+// With few pair tiles most SMs idle while a handful of clusters walk the whole K: at batch 8 the single-SM kernels (twice
+// the CTAs per layer) run the step in 0.560 ms against 0.593, at batch 32 it is a tie (0.791 / 0.782), from 64 on the pair
+// kernel wins (1.120 / 1.194).  B200RN_PAIR_MINITEMS (default 24 pair tiles x N tiles); B200RN_PAIR=2 ignores it (tests).
+static bool pair_items_ok(long m_tiles, int cout) {
+  const char* v = std::getenv("B200RN_PAIR");
+  if (v && v[0] == '2') return true;
+  const char* t = std::getenv("B200RN_PAIR_MINITEMS");
+  const long min_items = t ? std::max(1, std::atoi(t)) : 24;
+  const int block_n = cout % 256 == 0 ? 256 : 128;
+  return ((m_tiles + 1) / 2) * (cout / block_n) >= min_items;
+}
 
 static bool pdl_enabled() {
   static const bool on = !(std::getenv("B200RN_PDL") && std::getenv("B200RN_PDL")[0] == '0');
@@ -2236,7 +2247,8 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g_in, const void* 
     // layers the CTA-pair kernel takes (decided after plan_geometry below) do not go the "deep" way
     const bool pair_takes = pair_enabled() && !stem_mode && p.has_out && !p.has_res && !p.has_act && !p.has_pre && !p.out_f32 &&
                             g.kh * g.kw * (g.Cin / 64) >= pair_min_k() && pair_n_ok(g.Cout) &&
-                            long((g.Wo + pbw - 1) / pbw) * ((g.Ho + pbh - 1) / pbh) * ((g.B + pbn - 1) / pbn) >= 2 && sm_count() >= 2;
+                            long((g.Wo + pbw - 1) / pbw) * ((g.Ho + pbh - 1) / pbh) * ((g.B + pbn - 1) / pbn) >= 2 && sm_count() >= 2 &&
+                            pair_items_ok(long((g.Wo + pbw - 1) / pbw) * ((g.Ho + pbh - 1) / pbh) * ((g.B + pbn - 1) / pbn), g.Cout);
     const bool deep = !pair_takes && !(denv2 && denv2[0] == '0') && p.has_out && !p.has_res && !p.has_act && g.Cin >= 512 &&
                       g.Cout % kWideN == 0 && deep_tiles >= 2L * sm_count();
     if (!(wenv && wenv[0] == '0') && !stem_mode && !p.has_pre && g.kh == 1 && g.kw == 1 && g.pad == 0 && g.Cout % kWideN == 0 &&
@@ -2361,7 +2373,7 @@ UmmaConvPlan* umma_conv_plan_create(DType dt, const ConvGeom& g_in, const void* 
     const int m_tiles = p.tiles_w * p.tiles_h * ((g.B + bn - 1) / bn);
     const int sms = sm_count();
     if (pair_enabled() && !stem_mode && p.has_out && !p.has_res && !p.has_act && !p.has_pre && !p.out_f32 &&
-        p.num_k_iters >= pair_min_k() && pair_n_ok(g.Cout) && m_tiles >= 2 && sms >= 2) {
+        p.num_k_iters >= pair_min_k() && pair_n_ok(g.Cout) && m_tiles >= 2 && sms >= 2 && pair_items_ok(m_tiles, g.Cout)) {
       PairParams& pp = pl->pp;
       std::memset(&pp, 0, sizeof pp);
       pl->pair = 1;
