@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Condenses ncu reports / CSV logs into the small text files kept under profiles/.
     python tools/ncu_summary.py rep <file.ncu-rep> [...]      # key metrics per captured kernel (markdown)
-    python tools/ncu_summary.py launches <launches.csv> [traffic.json]   # per-launch time, DRAM bytes, tensor %
+    python tools/ncu_summary.py launches <launches.csv> [traffic.json|-] [label]   # per-launch time, DRAM bytes, tensor %
 """
 import csv
 import io
@@ -45,7 +45,7 @@ def rep(paths):
             print()
 
 
-def launches(path, traffic_json=None):
+def launches(path, traffic_json=None, label="fp16"):
     rows = [r for r in csv.reader(open(path)) if r and not r[0].startswith("==")]
     hdr = rows[0]
     iname, imet, iunit, ival, iid = (hdr.index("Kernel Name"), hdr.index("Metric Name"), hdr.index("Metric Unit"),
@@ -69,7 +69,7 @@ def launches(path, traffic_json=None):
 
     items = [per[k] for k in sorted(per)]
     tot = sum(d.get("gpu__time_duration.sum", 0.0) for d in items)
-    print("# ncu launch list: %d launches of one forward step (batch 256, fp16), %.1f us total\n" % (len(items), tot))
+    print("# ncu launch list: %d launches of one forward step (batch 256, %s), %.1f us total\n" % (len(items), label, tot))
     print("Cold-cache, serialised launches: compare SHARES with the CUDA-event numbers, not absolutes.\n")
     by = {}
     for d in items:
@@ -101,4 +101,4 @@ if __name__ == "__main__":
     if sys.argv[1] == "rep":
         rep(sys.argv[2:])
     else:
-        launches(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else None)
+        launches(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 and sys.argv[3] != "-" else None, sys.argv[4] if len(sys.argv) > 4 else "fp16")
