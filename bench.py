@@ -14,7 +14,7 @@ One replica per GPU, no data-path collective (the path shards by request: SURVEY
   e2e       the same metric through the public C-ABI call with HOST buffers: pinned host input ->
             cudaMemcpyAsync -> forward -> cudaMemcpyAsync -> pinned host output every step, using the
             double-buffered submit/wait entry points; wall clock, max over ranks.
-  roofline  the conv kernel (all 53 tcgen05 launches of a step): algorithmic conv FLOPs per step over
+  roofline  the conv kernels (all 47 tcgen05 conv launches of a step): algorithmic conv FLOPs per step over
             the sum of their CUDA-event durations, against the measured sustained bf16 peak.
   cpu_baseline  the CPU oracle (torch-CPU fp32, unfused; "port" -- ONNX Runtime is not on this image)
             on a bounded sample, all host threads.
@@ -439,7 +439,7 @@ def main():
             # TF32 products per algorithmic product, so frac <= 1/3 by construction
             pk = dict(pk, tflops=pk["tflops"] / 2, tflops_burst=pk["tflops_burst"] / 2,
                       source=pk["source"] + " / 2 for kind::tf32; 3 TF32 MMAs per algorithmic product")
-        roof = {"bound": "tensor", "kernel": "tcgen05 conv kernels (%d launches/step: conv_pair, conv_umma, conv_wide, conv_tail, conv_dualm, conv3x3_halo, stem7x7)" % len(conv),
+        roof = {"bound": "tensor", "kernel": "tcgen05 conv kernels (%d launches/step: conv_pair, conv_pairwide, conv_wide, conv_tail, conv_dualm, conv_umma, conv3x3_halo, conv3x3_halo2, stem7x7)" % len(conv),
                 "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
                 "peak_kind": "bf16_tflops_sustained", "peak_burst": pk["tflops_burst"], "frac_burst": achieved / pk["tflops_burst"],
                 "frac_sustained_leg": (sustained["images_per_s"] / world * FLOP_PER_IMAGE / 1e12 / pk["tflops"]) if sustained else None,
