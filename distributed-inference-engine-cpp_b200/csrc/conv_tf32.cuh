@@ -5,8 +5,10 @@
 // split exactly into hi = the value with its low 13 mantissa bits cleared and lo = value - hi (again cut to TF32), and
 //     a * w  ~=  a_hi * w_hi  +  a_hi * w_lo  +  a_lo * w_hi          (the dropped a_lo * w_lo is ~2^-22 relative)
 // The weights are split once on the host ([Cout][K] hi and lo arrays).  The activation tile arrives by TMA as raw fp32
-// and four transform warps split it in shared memory (hi in place, lo into a second buffer of the same swizzled layout)
-// before the MMA thread sees the stage.  Per K step of 8 channels three M128 x N x K8 instructions are issued:
+// and four transform warps write its lo part into a second buffer of the same swizzled layout before the MMA thread
+// sees the stage.  The raw tile itself serves as A_hi: the instruction ignores the low 13 mantissa bits of its operands,
+// which is exactly the cut that defines hi (measured: bit-for-bit the same op results as with hi written in place, and
+// a third less shared-memory traffic in the split; B200RN_TF32_RAW_HI=0 writes hi as the first version did).  Per K step of 8 channels three M128 x N x K8 instructions are issued:
 //     MAIN += A_hi * W_hi^T          LO += A_hi * W_lo^T          LO += A_lo * W_hi^T
 // Two-level accumulation.  The tensor core's fp32 accumulate truncates instead of rounding, a one-sided error of about
 // half an ulp per instruction that grows linearly with the length of the chain: measured 1.5e-5 relative at K = 2304
@@ -42,6 +44,7 @@ struct Tf32Params {
   const float* act_scale;
   const float* act_shift;
   const float* residual;          // fp32 NHWC [B, Ho, Wo, cout] or null
+  int raw_hi;                     // the transform warps leave the raw fp32 tile in place as A_hi (the MMA truncates it itself)
   int res_tma;                    // residual chunks arrive by TMA in a 16 KB buffer per epilogue group (one chunk ahead) instead of
                                   // per-thread global loads of 64-byte row pieces
 };
@@ -221,8 +224,10 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         const float4 a = lds_f4(a_hi + off);
         float4 h, l;
         h.x = tf32_hi(a.x); h.y = tf32_hi(a.y); h.z = tf32_hi(a.z); h.w = tf32_hi(a.w);
-        l.x = tf32_hi(a.x - h.x); l.y = tf32_hi(a.y - h.y); l.z = tf32_hi(a.z - h.z); l.w = tf32_hi(a.w - h.w);
-        sts_u4(a_hi + off, make_uint4(__float_as_uint(h.x), __float_as_uint(h.y), __float_as_uint(h.z), __float_as_uint(h.w)));
+        l.x = a.x - h.x; l.y = a.y - h.y; l.z = a.z - h.z; l.w = a.w - h.w;      // exact in fp32; the MMA cuts it to TF32 itself
+        // kind::tf32 ignores the low 13 mantissa bits of its operands, so the raw tile already IS A_hi to the MMA: only A_lo
+        // is written (raw_hi; a third less shared-memory traffic for the split)
+        if (!p.raw_hi) sts_u4(a_hi + off, make_uint4(__float_as_uint(h.x), __float_as_uint(h.y), __float_as_uint(h.z), __float_as_uint(h.w)));
         sts_u4(a_hi + A_BYTES + off, make_uint4(__float_as_uint(l.x), __float_as_uint(l.y), __float_as_uint(l.z), __float_as_uint(l.w)));
       }
       fence_proxy_async_smem();            // generic-proxy writes -> visible to the tensor core's reads

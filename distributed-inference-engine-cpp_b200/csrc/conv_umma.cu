@@ -2676,6 +2676,10 @@ Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g_in, const float* in, const
   p.num_stages = std::max(2, std::min(8, int((227u * 1024 - fixed) / stage_bytes)));
   pl->smem_bytes = fixed + uint32_t(p.num_stages) * stage_bytes;
   {
+    const char* rh = std::getenv("B200RN_TF32_RAW_HI");
+    p.raw_hi = !(rh && rh[0] == '0');
+  }
+  {
     // Residual by TMA into a 16 KB landing buffer per epilogue group, one chunk ahead, instead of per-thread global loads
     // of 64-byte row pieces -- also when the two buffers cost an operand stage.  Measured at batch 256 (exact mode):
     // residual + raw + activated layers 0.79 -> 0.72 (56x56), 0.44 -> 0.385 (28x28), 0.26 -> 0.24 ms (14x14); the

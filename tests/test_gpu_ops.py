@@ -45,6 +45,32 @@ def test_conv1x1_with_spatial_patches(dtype, name, kw, monkeypatch):
             assert r[key]["viol"] == 0, (name, key, r[key])
 
 
+def test_exact_mode_raw_tile_is_a_hi(monkeypatch):
+    """kind::tf32 ignores the low 13 mantissa bits of its operands, so the 3 x TF32 kernel leaves the raw fp32 activation
+    tile in place as A_hi and writes only A_lo.  With B200RN_TF32_RAW_HI=0 the transform warps write the masked hi as
+    the first version did: both must give the same bits."""
+    import numpy as np
+    import torch
+    g = torch.Generator().manual_seed(3)
+    B, H, W, Cin, Cout = 5, 14, 14, 128, 128
+    x = torch.randn(B, H, W, Cin, generator=g).cuda()
+    res = torch.randn(B, H, W, Cout, generator=g).cuda()
+    w = np.ascontiguousarray((torch.randn(Cout, 3, 3, Cin, generator=g) * 0.03).numpy())
+    bias = torch.randn(Cout, generator=g).numpy().astype(np.float32)
+    one, zero = np.ones(Cout, np.float32), np.zeros(Cout, np.float32)
+    outs = []
+    for raw in ("1", "0"):
+        monkeypatch.setenv("B200RN_TF32_RAW_HI", raw)
+        out = torch.full((B, H, W, Cout), float("nan"), device="cuda")
+        rc = gh.lib.b200rn_conv2d(0, x.data_ptr(), B, H, W, Cin, gh.pkg.fptr(w), gh.pkg.fptr(bias), Cout, 3, 3, 1, 1, 0,
+                                  res.data_ptr(), out.data_ptr(), None, gh.pkg.fptr(one), gh.pkg.fptr(zero), 1, None, None, 1)
+        assert rc == 0, gh.lib.b200rn_global_error()
+        torch.cuda.synchronize()
+        outs.append(out.cpu())
+    assert torch.isfinite(outs[0]).all()
+    assert torch.equal(outs[0], outs[1])
+
+
 RESIDUAL_CASES = [c for c in gh.CONV_CASES + gh.FP32_CASES if c[1].get("residual")]
 
 
