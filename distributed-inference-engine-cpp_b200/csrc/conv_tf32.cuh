@@ -17,6 +17,15 @@
 // buffers and the epilogue warps add every finished chunk into fp32 REGISTERS (N/2 per thread) with properly rounded
 // adds while the next chunk is being multiplied.  LO is 2^-11 of MAIN, its truncation error is negligible, and it stays
 // in tensor memory for the whole K (double-buffered across tiles).  v = registers + LO + bias.
+// Fused hi products (Tf32Params::fused, layers with >= 16 K blocks).  A_hi * W_hi^T and A_hi * W_lo^T read the same A
+// tile; stacking W_hi over W_lo (they are adjacent in a stage) makes them ONE instruction of width 2N whose result columns
+// are [MAIN | LO] side by side, so A_hi is read from shared memory once instead of twice per K step (20 KB instead of
+// 24 KB at N = 128, 14 instead of 18 KB at N = 64: these layers are bound by shared-memory bandwidth).  For that the LO
+// accumulator is tied to the MAIN buffer it sits beside -- tensor memory holds [MAIN0 | LO0 | MAIN1 | LO1], a chunk of
+// parity m accumulates its lo terms into LO_m and the epilogue adds LO0 + LO1 -- which gives up the double-buffering of
+// LO across tiles (the next tile's first MMA waits until the epilogue has read both; a few hundred cycles per tile, hence
+// only for long K).  The one instruction has one accumulate flag, and MAIN restarts at every chunk while LO_m carries on,
+// so the first K step of a chunk is issued as the three separate instructions.
 // Epilogue (two groups of 8 warps on alternating 32-channel chunks): bias, ReLU, residual, raw and/or BN-ReLU'd output
 // staged in swizzled shared memory (one buffer per output and group) and written by TMA stores, 32 channels (128 bytes)
 // per chunk.  The residual chunk arrives by TMA in a landing buffer per group, requested one chunk ahead by the group's
@@ -44,6 +53,8 @@ struct Tf32Params {
   const float* act_scale;
   const float* act_shift;
   const float* residual;          // fp32 NHWC [B, Ho, Wo, cout] or null
+  int fused;                      // one MMA of width 2N per K step for both A_hi products ([MAIN_m | LO_m] side by side in tensor memory):
+                                  // see "Fused hi products" above; needs raw_hi-style operands only in that W_lo follows W_hi in the stage
   int raw_hi;                     // the transform warps leave the raw fp32 tile in place as A_hi (the MMA truncates it itself)
   int res_tma;                    // residual chunks arrive by TMA in a 16 KB buffer per epilogue group (one chunk ahead) instead of
                                   // per-thread global loads of 64-byte row pieces
@@ -176,11 +187,14 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       int stage = 0;
       uint32_t phase = 0;
       uint32_t chunk = 0;                   // running MAIN chunk counter over all of this CTA's tiles
+      constexpr uint32_t idesc2 = make_idesc_tf32<(2 * BLOCK_N <= 256 ? 2 * BLOCK_N : BLOCK_N)>();
       for (int i = 0; i < my_tiles; ++i) {
-        const int lbuf = i & 1;
-        mbar_wait(smem_u32(&lo_empty[lbuf]), ((uint32_t(i) >> 1) & 1) ^ 1);
+        // fused: one LO pair for all tiles (barrier 0, a phase per tile); otherwise LO double-buffered across tiles
+        const int lbuf = p.fused ? 0 : (i & 1);
+        const uint32_t lo_parity = p.fused ? (uint32_t(i) & 1) : ((uint32_t(i) >> 1) & 1);
+        mbar_wait(smem_u32(&lo_empty[lbuf]), lo_parity ^ 1);
         tc_fence_after();
-        const uint32_t tmem_lo = tmem_base + uint32_t(2 + lbuf) * BLOCK_N;
+        uint32_t tile_chunk = 0;            // MAIN chunk index within this tile
         for (int it = 0; it < p.num_k_iters; ++it) {
           const int in_chunk = it % kT32ChunkBlocks;
           const uint32_t mbuf = chunk & 1;
@@ -188,22 +202,30 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             mbar_wait(smem_u32(&main_empty[mbuf]), ((chunk >> 1) & 1) ^ 1);   // the epilogue has taken this buffer's last chunk
             tc_fence_after();
           }
-          const uint32_t tmem_main = tmem_base + mbuf * BLOCK_N;
+          // tensor memory: [MAIN0 | MAIN1 | LO0 | LO1], or fused [MAIN0 | LO0 | MAIN1 | LO1]
+          const uint32_t tmem_main = tmem_base + (p.fused ? 2 * mbuf : mbuf) * BLOCK_N;
+          const uint32_t tmem_lo = p.fused ? tmem_main + BLOCK_N : tmem_base + uint32_t(2 + lbuf) * BLOCK_N;
           mbar_wait(smem_u32(&xf_bar[stage]), phase);
           tc_fence_after();
           const uint32_t ahi = pipe_lo + uint32_t(stage) * (STAGE_BYTES >> 4);
           const uint32_t alo = ahi + (A_BYTES >> 4);
           const uint32_t bhi = ahi + 2 * (A_BYTES >> 4);
           const uint32_t blo = bhi + (B_BYTES >> 4);
+          // lo terms: the first instruction into an LO buffer within a tile overwrites it
+          const bool lo_first = p.fused ? (tile_chunk < 2 && in_chunk == 0) : (it == 0);
 #pragma unroll
           for (int k = 0; k < 4; ++k) {       // K = 8 fp32 = 32 bytes per instruction
-            umma_tf32_lo(tmem_main, ahi + 2 * k, bhi + 2 * k, desc_hi, idesc, (in_chunk | k) != 0 ? 1u : 0u);
-            umma_tf32_lo(tmem_lo, ahi + 2 * k, blo + 2 * k, desc_hi, idesc, (it | k) != 0 ? 1u : 0u);
+            if (p.fused && (in_chunk | k) != 0) {
+              umma_tf32_lo(tmem_main, ahi + 2 * k, bhi + 2 * k, desc_hi, idesc2, 1u);      // [MAIN | LO] += A_hi * [W_hi ; W_lo]^T
+            } else {
+              umma_tf32_lo(tmem_main, ahi + 2 * k, bhi + 2 * k, desc_hi, idesc, (in_chunk | k) != 0 ? 1u : 0u);
+              umma_tf32_lo(tmem_lo, ahi + 2 * k, blo + 2 * k, desc_hi, idesc, (lo_first && k == 0) ? 0u : 1u);
+            }
             umma_tf32_lo(tmem_lo, alo + 2 * k, bhi + 2 * k, desc_hi, idesc, 1u);
           }
           umma_commit(smem_u32(&empty_bar[stage]));
           const bool last = it == p.num_k_iters - 1;
-          if (in_chunk == kT32ChunkBlocks - 1 || last) { umma_commit(smem_u32(&main_full[mbuf])); ++chunk; }
+          if (in_chunk == kT32ChunkBlocks - 1 || last) { umma_commit(smem_u32(&main_full[mbuf])); ++chunk; ++tile_chunk; }
           if (last) umma_commit(smem_u32(&lo_full[lbuf]));
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
@@ -295,7 +317,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 #pragma unroll
         for (int j = 0; j < kGroupChunks; ++j) {
           uint32_t d[16];
-          tmem_ld_32x32b_x16(lane_addr + mbuf * BLOCK_N + uint32_t((grp + 2 * j) * 32 + g * 16), d);
+          tmem_ld_32x32b_x16(lane_addr + (p.fused ? 2 * mbuf : mbuf) * BLOCK_N + uint32_t((grp + 2 * j) * 32 + g * 16), d);
           tmem_ld_wait();
 #pragma unroll
           for (int k = 0; k < 16; ++k) sum[j * 16 + k] += __uint_as_float(d[k]);
@@ -304,14 +326,25 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&main_empty[mbuf]));
       }
-      mbar_wait(smem_u32(&lo_full[buf]), (uint32_t(i) >> 1) & 1);
+      // lo terms: one accumulator per tile parity, or (fused) LO0 + LO1 of the single pair, a barrier phase per tile
+      const int lbar = p.fused ? 0 : buf;
+      mbar_wait(smem_u32(&lo_full[lbar]), p.fused ? (uint32_t(i) & 1) : ((uint32_t(i) >> 1) & 1));
       tc_fence_after();
 #pragma unroll
       for (int j = 0; j < kGroupChunks; ++j, ++cc) {
         const int c = grp + 2 * j;
         const int ch0 = c * 32 + g * 16;            // first of this thread's 16 channels within the N tile
         uint32_t d1[16];
-        tmem_ld_32x32b_x16(lane_addr + uint32_t(2 + buf) * BLOCK_N + uint32_t(ch0), d1);
+        if (p.fused) {
+          uint32_t d2[16];
+          tmem_ld_32x32b_x16(lane_addr + uint32_t(BLOCK_N + ch0), d1);
+          tmem_ld_32x32b_x16(lane_addr + uint32_t(3 * BLOCK_N + ch0), d2);
+          tmem_ld_wait();
+#pragma unroll
+          for (int k = 0; k < 16; ++k) d1[k] = __float_as_uint(__uint_as_float(d1[k]) + __uint_as_float(d2[k]));
+        } else {
+          tmem_ld_32x32b_x16(lane_addr + uint32_t(2 + buf) * BLOCK_N + uint32_t(ch0), d1);
+        }
         float4 bv[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) bv[k] = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + ch0) + k);
@@ -319,7 +352,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         if (j == kGroupChunks - 1) {        // this warp's part of the LO accumulator is read: hand it back to the MMA thread
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(smem_u32(&lo_empty[buf]));
+          if (lane == 0) mbar_arrive(smem_u32(&lo_empty[lbar]));
         }
         if (store_thread && cc > 0) tma_store_wait_read();   // the group's previous stores have read its staging buffers
         asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory");

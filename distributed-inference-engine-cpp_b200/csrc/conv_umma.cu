@@ -2678,6 +2678,13 @@ Tf32ConvPlan* tf32_conv_plan_create(const ConvGeom& g_in, const float* in, const
   {
     const char* rh = std::getenv("B200RN_TF32_RAW_HI");
     p.raw_hi = !(rh && rh[0] == '0');
+    // Both A_hi products as one instruction of width 2N: for the 3x3 convs (18-144 K blocks).  Measured at batch 256:
+    // 3x3 layers 0.305 -> 0.293 (N = 128), 0.446 -> 0.424 ms (N = 64); the 1x1 layers with 16-32 K blocks lose 5-10 %
+    // (the next tile's first MMA waits for the epilogue to read the single LO pair), so they keep the three-instruction
+    // form.  B200RN_TF32_FUSED=0 off, =N smallest K-block count of a 3x3 layer (default 16), negative: any filter size.
+    const char* fe = std::getenv("B200RN_TF32_FUSED");
+    const int fmin = fe ? std::atoi(fe) : 16;
+    p.fused = !stem && fmin != 0 && (fmin < 0 || g.kh * g.kw >= 9) && p.num_k_iters >= std::max(2 * kT32ChunkBlocks, std::abs(fmin));
   }
   {
     // Residual by TMA into a 16 KB landing buffer per epilogue group, one chunk ahead, instead of per-thread global loads

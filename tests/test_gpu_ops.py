@@ -71,6 +71,24 @@ def test_exact_mode_raw_tile_is_a_hi(monkeypatch):
     assert torch.equal(outs[0], outs[1])
 
 
+LONG_K_CASES = [c for c in gh.CONV_CASES + gh.FP32_CASES
+                if c[1]["k"] * c[1]["k"] * (c[1]["Cin"] // 32) >= 8 and c[1]["Cin"] % 32 == 0 and c[1]["Cout"] % 64 == 0]
+
+
+@pytest.mark.parametrize("fused", ["0", "-8"], ids=["three-instructions", "fused-any-filter"])
+@pytest.mark.parametrize("name,kw", LONG_K_CASES, ids=[c[0] for c in LONG_K_CASES])
+def test_conv2d_exact_mode_hi_product_forms(name, kw, fused, monkeypatch):
+    """3 x TF32 kernel: A_hi * W_hi and A_hi * W_lo as one MMA of width 2N (default for 3x3 convs with >= 16 K blocks) or
+    as two.  B200RN_TF32_FUSED=0 forces the three-instruction form everywhere, -8 the fused one for every layer with
+    at least 8 K blocks, 1x1 included."""
+    monkeypatch.setenv("B200RN_TF32_FUSED", fused)
+    r = gh.conv_case(0, **kw)
+    assert r["rc"] == 0, r["msg"]
+    for key in ("out", "act"):
+        if key in r:
+            assert r[key]["viol"] == 0, (name, key, r[key])
+
+
 RESIDUAL_CASES = [c for c in gh.CONV_CASES + gh.FP32_CASES if c[1].get("residual")]
 
 
